@@ -1,0 +1,120 @@
+"""akarirender-1_b200 — B200-native backend for AkariRender's Path-integrator hot path.
+
+The product is libakari_b200.so (csrc/, hand-written sm_100a CUDA behind the C ABI of include/akari_b200.h).
+This package is the thin host-side mirror used by tests and bench.py: the reference's node vocabulary
+(`nodes`), synthetic scenes of the BASELINE shapes (`scenes`) and `Backend`, which drives the C ABI through
+ctypes. There is no CPU fallback: everything here fails loudly if the CUDA library is missing.
+
+(The directory name is not a Python identifier; import it with importlib.import_module("akarirender-1_b200").)
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import abi, nodes, scenes  # noqa: F401
+
+HIT_DTYPE = np.dtype([("t", np.float32), ("u", np.float32), ("v", np.float32), ("prim_id", np.int32),
+                      ("geom_id", np.int32)])
+
+
+class AkariError(RuntimeError):
+    pass
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+_initialised = None
+
+
+def init(device_index=0):
+    """akb_init: bind this process to one GPU (one process per GPU)."""
+    global _initialised
+    lib = abi.load()
+    if _initialised != device_index:
+        _check(lib, lib.akb_init(device_index))
+        _initialised = device_index
+    return lib
+
+
+def _check(lib, rc):
+    if rc != abi.OK:
+        raise AkariError(f"akb status {rc}: {lib.akb_last_error().decode(errors='replace')}")
+
+
+class Backend:
+    """A committed scene on the device: the replacement for `scene.accel = BVHAccelerator; scene.commit()` +
+    `gpu::Integrator::render` (core/nodes/scene.cpp:119-162)."""
+
+    def __init__(self, scene, device_index=0):
+        self.lib = init(device_index)
+        self.scene = scene
+        self.width, self.height = scene.camera.resolution
+        desc, keep = scene.flatten()
+        h = C.c_void_p()
+        _check(self.lib, self.lib.akb_scene_create(C.byref(desc), C.byref(h)))
+        self.h = h
+        del keep  # the library deep-copies
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.akb_scene_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self):
+        keys = ["n_triangles", "n_bvh_nodes", "bvh_bytes", "n_lights", "triangle_bytes"]
+        return {k: int(self.lib.akb_scene_info(self.h, i)) for i, k in enumerate(keys)}
+
+    # ---- Scene::intersect / occlude over host ray batches
+    def trace(self, org_tmin, dir_tmax, any_hit=False):
+        org = np.ascontiguousarray(org_tmin, np.float32)
+        dr = np.ascontiguousarray(dir_tmax, np.float32)
+        n = org.shape[0]
+        hits = np.zeros(n, HIT_DTYPE)
+        occ = np.zeros(n, np.int32)
+        _check(self.lib, self.lib.akb_trace(self.h, _ptr(org), _ptr(dr), n, int(any_hit), _ptr(hits), _ptr(occ)))
+        return occ if any_hit else hits
+
+    def trace_device(self, d_org, d_dir, n, any_hit, d_hits, d_occ, stream=0):
+        """Device pointers (ints). Returns the traversal kernel's device time in ms."""
+        ms = C.c_float(0)
+        _check(self.lib, self.lib.akb_trace_device(self.h, d_org, d_dir, n, int(any_hit), d_hits, d_occ, stream,
+                                                   C.byref(ms)))
+        return ms.value
+
+    def generate_rays(self, xy, u2):
+        xy = np.ascontiguousarray(xy, np.int32)
+        u2 = np.ascontiguousarray(u2, np.float32)
+        n = xy.shape[0]
+        org = np.zeros((n, 4), np.float32)
+        dr = np.zeros((n, 4), np.float32)
+        _check(self.lib, self.lib.akb_generate_rays(self.h, _ptr(xy), _ptr(u2), n, _ptr(org), _ptr(dr)))
+        return org, dr
+
+    # ---- Integrator::render
+    def render(self, params=None, out=None):
+        """Host film (H, W, 4) float32 = (sum R, sum G, sum B, sum weight). Returns (film, stats)."""
+        p = params if params is not None else self.scene.integrator.params()
+        film = out if out is not None else np.zeros((self.height, self.width, 4), np.float32)
+        st = abi.RenderStats()
+        _check(self.lib, self.lib.akb_render(self.h, C.byref(p), _ptr(film), C.byref(st)))
+        return film, st
+
+    def render_device(self, d_film, params=None, stream=0):
+        p = params if params is not None else self.scene.integrator.params()
+        st = abi.RenderStats()
+        _check(self.lib, self.lib.akb_render_device(self.h, C.byref(p), d_film, stream, C.byref(st)))
+        return st
+
+    def film_to_srgb8(self, film):
+        h, w = film.shape[:2]
+        out = np.zeros((h, w, 3), np.uint8)
+        _check(self.lib, self.lib.akb_film_to_srgb8(_ptr(np.ascontiguousarray(film, np.float32)), w, h, _ptr(out)))
+        return out

@@ -1,0 +1,195 @@
+/*
+ * akari_b200.h — C ABI of the B200-native path-tracing backend (libakari_b200.so).
+ *
+ * This is the drop-in boundary for ONE hot path of AkariRender: BVH ray/scene intersection +
+ * the unidirectional `Path` integrator bounce loop + Film accumulation.
+ * Every entry point below names the reference interface it replaces (paths relative to
+ * /root/reference/src/akari/). Plain pointers and sizes only; no C++/torch types cross the ABI;
+ * no exceptions and no abort(): every call returns an akb_status and leaves a message
+ * retrievable with akb_last_error() (reference behaviour being replaced: CUDA_CHECK ->
+ * fatal()+abort(), kernel/cuda/util.h:28-36).
+ *
+ * There is NO CPU fallback behind this ABI. Without a CUDA device akb_init() returns
+ * AKB_NO_DEVICE and every compute call fails loudly.
+ */
+#ifndef AKARI_B200_H
+#define AKARI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AKB_ABI_VERSION 1
+
+typedef enum akb_status {
+    AKB_OK = 0,
+    AKB_INVALID_ARG = 1,
+    AKB_CUDA_ERROR = 2,
+    AKB_NCCL_ERROR = 3,
+    AKB_OOM = 4,
+    AKB_NO_DEVICE = 5
+} akb_status;
+
+/* ---- flattened Scene<C> (kernel/scene.h:50-91, kernel/instance.h:30-35) -------------------- */
+
+/* Material variant tags, kernel/material.h:244-246 (Diffuse, Glossy, Emissive, Mix);
+ * DIELECTRIC is an extension the reference does not have. */
+typedef enum akb_material_type {
+    AKB_MAT_DIFFUSE = 0,
+    AKB_MAT_GLOSSY = 1,
+    AKB_MAT_EMISSIVE = 2,
+    AKB_MAT_MIX = 3,
+    AKB_MAT_DIELECTRIC = 4
+} akb_material_type;
+
+/* One entry of the scene-wide material table. Textures are constant RGB (kernel/texture.h:30-37),
+ * which is what every BASELINE config uses. */
+typedef struct akb_material {
+    int32_t type;         /* akb_material_type */
+    float color[3];       /* Diffuse/Glossy reflectance, Emissive radiance, Dielectric tint */
+    float roughness;      /* Glossy: texture value r; alpha = r*r (kernel/material.h:225-226) */
+    float fraction;       /* Mix: u < fraction selects child_b (kernel/material.h:255-268) */
+    int32_t child_a;      /* Mix: `first`  -> material_A, index into the scene material table */
+    int32_t child_b;      /* Mix: `second` -> material_B */
+    int32_t double_sided; /* Emissive (core/nodes/material.cpp never sets it -> 0) */
+    float ior;            /* Dielectric (extension) */
+} akb_material;
+
+/* One MeshInstance (kernel/instance.h:30-35); array layout = the .mesh file's (core/mesh.cpp:48-85). */
+typedef struct akb_mesh {
+    uint64_t n_vertices;
+    uint64_t n_triangles;
+    const float *vertices;           /* 3*n_vertices */
+    const float *normals;            /* 9*n_triangles, per corner */
+    const float *texcoords;          /* 6*n_triangles, per corner */
+    const int32_t *indices;          /* 3*n_triangles */
+    const int32_t *material_indices; /* n_triangles, index into `materials` below; -1 = none */
+    const int32_t *materials;        /* n_mesh_materials indices into akb_scene_desc.materials */
+    int32_t n_mesh_materials;
+    int32_t _pad;
+} akb_mesh;
+
+/* PerspectiveCamera(resolution, c2w, fov) (kernel/camera.h:36-66). c2w is row-major 4x4, built by the
+ * caller as core/nodes/camera.cpp:32-39 does; r2c is derived inside the library exactly as
+ * kernel/camera.h:45-59 (including s = atan(fov/2)). */
+typedef struct akb_camera {
+    float c2w[16];
+    float fov; /* radians */
+    int32_t width;
+    int32_t height;
+    float lens_radius;    /* no reference node sets these; must be 0 */
+    float focal_distance;
+} akb_camera;
+
+typedef struct akb_scene_desc {
+    uint32_t abi_version; /* AKB_ABI_VERSION */
+    uint32_t n_meshes;
+    const akb_mesh *meshes;
+    uint32_t n_materials;
+    uint32_t _pad;
+    const akb_material *materials;
+    akb_camera camera;
+} akb_scene_desc;
+
+/* ---- integrator parameters (kernel/integrators/gpu/integrator.h:39-53, core/nodes/integrator.cpp:26-84) */
+
+typedef enum akb_integrator { AKB_INTEGRATOR_PATH = 0, AKB_INTEGRATOR_AO = 1 } akb_integrator;
+typedef enum akb_sampler { AKB_SAMPLER_LCG = 0, AKB_SAMPLER_PCG = 1 } akb_sampler; /* kernel/sampler.h:28-66 */
+typedef enum akb_mode { AKB_MODE_WAVEFRONT = 0, AKB_MODE_MEGAKERNEL = 1 } akb_mode; /* Path{wavefront|megakernel} */
+
+typedef struct akb_render_params {
+    int32_t integrator;     /* akb_integrator */
+    int32_t spp;            /* Path.spp / AO.spp */
+    int32_t max_depth;      /* Path.max_depth (CPU oracle hard-codes 5, cpu/integrator.cpp:91) */
+    float ray_clamp;        /* >0: per-sample clamp to [0, ray_clamp] + NaN->0 as gpu/cuda/integrator.cpp:196-198;
+                               0: off (CPU-oracle semantics) */
+    int32_t sampler;        /* akb_sampler; the reference hard-wires LCG (core/nodes/scene.cpp:126) */
+    int32_t rr_start_depth; /* 0 = off (reference); >0: Russian roulette from this depth (extension) */
+    int32_t mode;           /* akb_mode */
+    int32_t sort_materials; /* wavefront: order the shading wave by material id */
+    float ao_occlude;       /* AO.occlude distance */
+    /* image-space sharding: interleaved tile_size^2 tiles, owner = tile_id % world_size.
+       Pixels this rank does not own are left at zero in the film. */
+    int32_t rank;
+    int32_t world_size;
+    int32_t tile_size;
+} akb_render_params;
+
+/* Per-render statistics (the reference prints per-kernel cudaEvent stats, kernel/cuda/launch.cpp:92-118). */
+typedef struct akb_render_stats {
+    uint64_t n_samples;       /* camera paths started */
+    uint64_t n_closest_rays;  /* Scene::intersect queries */
+    uint64_t n_shadow_rays;   /* Scene::occlude queries */
+    uint64_t n_kernel_launches;
+    float ms_total;           /* device time of the whole render (CUDA events) */
+    float ms_raygen, ms_extend, ms_shade, ms_shadow, ms_film, ms_sort; /* per-stage device time when profiled */
+} akb_render_stats;
+
+/* Result of Scene::intersect (kernel/scene.h:40-49): prim_id/geom_id = -1 and t = +inf on a miss. */
+typedef struct akb_hit {
+    float t, u, v;
+    int32_t prim_id;
+    int32_t geom_id;
+} akb_hit;
+
+typedef struct akb_scene akb_scene; /* opaque */
+
+/* ---- lifecycle --------------------------------------------------------------------------------------- */
+
+/* Replaces Device selection (cmd/akari.cpp:41-76 `--gpu`, core/device.cpp:142-183). Binds this process to
+ * CUDA device `device_index` (one process per GPU). */
+akb_status akb_init(int device_index);
+akb_status akb_shutdown(void);
+const char *akb_last_error(void);
+/* 0 when no CUDA device is usable. */
+int akb_device_count(void);
+
+/* Replaces SceneNode::compile + `scene.accel = BVHAccelerator; scene.commit()` (core/nodes/scene.cpp:43-95,
+ * 119-135; kernel/scene.cpp:64-81; kernel/bvh-accelerator.h:671-678): deep-copies the description, derives the
+ * area-light list and power distribution, builds the compressed 8-wide BVH and uploads everything to HBM. */
+akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene);
+akb_status akb_scene_destroy(akb_scene *scene);
+
+/* Scene facts (for tests/benches): 0 n_triangles, 1 n_bvh_nodes, 2 bvh_bytes, 3 n_lights, 4 triangle_bytes. */
+uint64_t akb_scene_info(const akb_scene *scene, int what);
+
+/* ---- the hot path ------------------------------------------------------------------------------------ */
+
+/* Replaces gpu::Integrator<C>::render(const Scene<C>&, Film<C>*) (kernel/integrators/gpu/integrator.h:54-59,
+ * called from SceneNode::render core/nodes/scene.cpp:141-162). Blocking. `out_rgbw` is a HOST buffer of
+ * width*height*4 floats = (sum R, sum G, sum B, sum weight) per pixel, row-major: the contents of
+ * Film::radiance / Film::weight after merge_tile (core/film.h:66-95). `stats` may be NULL. */
+akb_status akb_render(akb_scene *scene, const akb_render_params *params, float *out_rgbw, akb_render_stats *stats);
+
+/* Same, but the film stays in HBM: `d_out_rgbw` is a DEVICE pointer (width*height*4 floats) the caller owns
+ * (e.g. a buffer it will hand to NCCL). Work is enqueued on `cuda_stream` (a cudaStream_t, 0 = default) and
+ * the call returns after the stream has been synchronised. */
+akb_status akb_render_device(akb_scene *scene, const akb_render_params *params, float *d_out_rgbw,
+                             void *cuda_stream, akb_render_stats *stats);
+
+/* Replaces Scene::intersect / Scene::occlude (kernel/scene.h:58-67) over a batch of rays.
+ * Rays are two float4 streams (vectorised SoA): org_tmin[i] = (ox,oy,oz,tmin), dir_tmax[i] = (dx,dy,dz,tmax).
+ * any_hit = 0: closest hit -> out_hits[i]; any_hit = 1: out_occluded[i] = 0/1. HOST pointers. */
+akb_status akb_trace(akb_scene *scene, const float *org_tmin, const float *dir_tmax, size_t n_rays, int any_hit,
+                     akb_hit *out_hits, int32_t *out_occluded);
+/* DEVICE-pointer variant of akb_trace; `ms_kernel` (may be NULL) receives the traversal kernel's device time. */
+akb_status akb_trace_device(akb_scene *scene, const float *d_org_tmin, const float *d_dir_tmax, size_t n_rays,
+                            int any_hit, akb_hit *d_out_hits, int32_t *d_out_occluded, void *cuda_stream,
+                            float *ms_kernel);
+
+/* Replaces Camera::generate_ray (kernel/camera.h:67-86) for a batch: pixel (x,y) with lens sample u1 (unused,
+ * pinhole) and film sample u2. HOST pointers; writes the two float4 ray streams. Test/KAT helper. */
+akb_status akb_generate_rays(akb_scene *scene, const int32_t *xy, const float *u2, size_t n, float *org_tmin,
+                             float *dir_tmax);
+
+/* Film post-process of Film::write_image (core/film.h:97-113, core/image.cpp:38-61): radiance/weight ->
+ * sRGB OETF -> round(255.5*x) clamp -> RGB8. HOST pointers; runs on the device. */
+akb_status akb_film_to_srgb8(const float *rgbw, int32_t width, int32_t height, uint8_t *out_rgb8);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AKARI_B200_H */

@@ -1,0 +1,312 @@
+// oracle/ref_harness.cpp — TEST INFRASTRUCTURE ONLY. Not part of the product path.
+//
+// Thin C-ABI driver around the UNMODIFIED reference kernel headers, compiled in place from
+// /root/reference/src (see oracle/Makefile). It takes the same flattened scene description the product
+// library takes (include/akari_b200.h) and runs the reference's own code on it:
+//   * Scene<C> + BVHAccelerator<C> build/intersect/occlude   (kernel/scene.{h,cpp}, kernel/bvh-accelerator.h)
+//   * PerspectiveCamera<C>::generate_ray                      (kernel/camera.h:67-86)
+//   * GenericPathTracer<C>::run_megakernel                    (kernel/pathtracer.h:136-163)
+// The only logic restated here (because it lives in the node layer, which needs the SDL parser and image IO to
+// compile) is the 30-line light-list / power-distribution loop of SceneNode::compile (core/nodes/scene.cpp:51-92)
+// and the per-pixel sampling loop of cpu::PathTracer::render (kernel/integrators/cpu/integrator.cpp:115-135) —
+// the latter because Film keeps its float buffers private and can only write 8-bit PNG (core/film.h:76-113).
+// Built into oracle/_ref/libakari_ref.so (git-ignored). Used by tests/ (as the checker), tests/golden/make_golden.py
+// and bench.py's `--impl reference` / cpu_baseline legs only.
+#include <akari/kernel/scene.h>
+#include <akari/kernel/bvh-accelerator.h>
+#include <akari/kernel/pathtracer.h>
+#include <akari/core/device.h>
+
+#include <atomic>
+#include <cstring>
+#include <memory>
+#include <thread>
+#include <vector>
+
+#include "../include/akari_b200.h"
+
+using namespace akari;
+using C = Config<float, Color<float, 3>>;
+
+namespace {
+    struct RefScene {
+        AKR_IMPORT_TYPES()
+        std::vector<std::vector<float>> P, N, UV;
+        std::vector<std::vector<int>> I, MI;
+        std::vector<std::vector<const Material<C> *>> mesh_mats;
+        std::vector<std::unique_ptr<Texture<C>>> textures;
+        std::vector<Material<C> *> materials; // scene table
+        std::vector<MeshInstance<C>> instances;
+        std::vector<AreaLight<C>> lights;
+        std::unique_ptr<Distribution1D<C>> light_distribution;
+        std::unique_ptr<BVHAccelerator<C>> accel;
+        Scene<C> scene;
+        int width = 0, height = 0;
+        ~RefScene() {
+            for (auto *m : materials)
+                ::operator delete(m);
+        }
+        Texture<C> *tex(float r, float g, float b) {
+            textures.emplace_back(new Texture<C>(ConstantTexture<C>(Spectrum(r, g, b))));
+            return textures.back().get();
+        }
+    };
+
+    thread_local std::string g_err;
+
+    // core/nodes/scene.cpp:51-92 restated with the reference's own types.
+    void build_lights(RefScene &rs) {
+        AKR_IMPORT_TYPES()
+        auto &scene = rs.scene;
+        std::vector<Float> power;
+        for (uint32_t mesh_id = 0; mesh_id < scene.meshes.size(); mesh_id++) {
+            MeshInstance<C> &mesh = scene.meshes[mesh_id];
+            for (uint32_t prim_id = 0; prim_id < mesh.indices.size() / 3; prim_id++) {
+                auto triangle = scene.get_triangle(mesh_id, prim_id);
+                auto material = triangle.material;
+                if (!material)
+                    continue;
+                if (material->template isa<EmissiveMaterial<C>>())
+                    rs.lights.emplace_back(triangle);
+            }
+        }
+        for (size_t i = 0; i < rs.lights.size(); i++) {
+            auto &light = rs.lights[i];
+            // Texture::integral() (kernel/texture.h:63-65) does not compile under g++ 13 (dependent-base lookup);
+            // every texture here is constant, so call ConstantTexture::integral (kernel/texture.h:36) directly.
+            auto I = light.color->template get<ConstantTexture<C>>()->integral();
+            auto &triangle = light.triangle;
+            Float3 tc[3];
+            for (int j = 0; j < 3; j++)
+                tc[j] = Float3(triangle.texcoords[j].x, triangle.texcoords[j].y, 0.0);
+            auto tc_area = length(cross(tc[1] - tc[0], tc[2] - tc[0])) * 0.5;
+            auto area =
+                length(cross(triangle.vertices[1] - triangle.vertices[0], triangle.vertices[2] - triangle.vertices[0]));
+            power.emplace_back(area * tc_area * I);
+        }
+        rs.light_distribution.reset(new Distribution1D<C>(default_resource(), power.data(), power.size()));
+        scene.light_distribution = rs.light_distribution.get();
+        scene.area_lights = BufferView<AreaLight<C>>(rs.lights.data(), rs.lights.size());
+    }
+} // namespace
+
+extern "C" {
+
+const char *akref_last_error(void) { return g_err.c_str(); }
+
+void *akref_scene_create(const akb_scene_desc *d) {
+    AKR_IMPORT_TYPES()
+    try {
+        if (!d || d->abi_version != AKB_ABI_VERSION) {
+            g_err = "bad desc";
+            return nullptr;
+        }
+        set_device_cpu(); // cmd/akari.cpp:41-76 does this before anything allocates (default_resource())
+        auto rs = std::make_unique<RefScene>();
+        // materials: allocate raw storage first so Mix children can point at any entry
+        rs->materials.resize(d->n_materials, nullptr);
+        for (uint32_t i = 0; i < d->n_materials; i++)
+            rs->materials[i] = (Material<C> *)::operator new(sizeof(Material<C>));
+        for (uint32_t i = 0; i < d->n_materials; i++) {
+            const akb_material &m = d->materials[i];
+            switch (m.type) {
+            case AKB_MAT_DIFFUSE:
+                new (rs->materials[i]) Material<C>(DiffuseMaterial<C>(rs->tex(m.color[0], m.color[1], m.color[2])));
+                break;
+            case AKB_MAT_GLOSSY:
+                new (rs->materials[i]) Material<C>(GlossyMaterial<C>(rs->tex(m.color[0], m.color[1], m.color[2]),
+                                                                     rs->tex(m.roughness, m.roughness, m.roughness)));
+                break;
+            case AKB_MAT_EMISSIVE:
+                new (rs->materials[i])
+                    Material<C>(EmissiveMaterial<C>(rs->tex(m.color[0], m.color[1], m.color[2]), m.double_sided != 0));
+                break;
+            case AKB_MAT_MIX:
+                if (m.child_a < 0 || m.child_b < 0 || (uint32_t)m.child_a >= d->n_materials ||
+                    (uint32_t)m.child_b >= d->n_materials) {
+                    g_err = "mix child out of range";
+                    return nullptr;
+                }
+                new (rs->materials[i]) Material<C>(MixMaterial<C>(rs->tex(m.fraction, m.fraction, m.fraction),
+                                                                  rs->materials[m.child_a], rs->materials[m.child_b]));
+                break;
+            default:
+                g_err = "material type not representable in the reference (extension)";
+                return nullptr;
+            }
+        }
+        size_t nm = d->n_meshes;
+        rs->P.resize(nm), rs->N.resize(nm), rs->UV.resize(nm), rs->I.resize(nm), rs->MI.resize(nm);
+        rs->mesh_mats.resize(nm);
+        rs->instances.resize(nm);
+        for (size_t k = 0; k < nm; k++) {
+            const akb_mesh &m = d->meshes[k];
+            rs->P[k].assign(m.vertices, m.vertices + 3 * m.n_vertices);
+            rs->N[k].assign(m.normals, m.normals + 9 * m.n_triangles);
+            rs->UV[k].assign(m.texcoords, m.texcoords + 6 * m.n_triangles);
+            rs->I[k].assign(m.indices, m.indices + 3 * m.n_triangles);
+            rs->MI[k].assign(m.material_indices, m.material_indices + m.n_triangles);
+            for (int j = 0; j < m.n_mesh_materials; j++)
+                rs->mesh_mats[k].push_back(rs->materials[m.materials[j]]);
+            MeshInstance<C> &inst = rs->instances[k];
+            inst.vertices = BufferView<float>(rs->P[k].data(), rs->P[k].size());
+            inst.normals = BufferView<float>(rs->N[k].data(), rs->N[k].size());
+            inst.texcoords = BufferView<float>(rs->UV[k].data(), rs->UV[k].size());
+            inst.indices = BufferView<int>(rs->I[k].data(), rs->I[k].size());
+            inst.material_indices = BufferView<int>(rs->MI[k].data(), rs->MI[k].size());
+            inst.materials = BufferView<const Material<C> *>(rs->mesh_mats[k].data(), rs->mesh_mats[k].size());
+        }
+        Scene<C> &scene = rs->scene;
+        scene.meshes = BufferView<MeshInstance<C>>(rs->instances.data(), rs->instances.size());
+        float cm[16];
+        std::memcpy(cm, d->camera.c2w, sizeof(cm));
+        Transform3f c2w{Matrix4f(cm)};
+        rs->width = d->camera.width, rs->height = d->camera.height;
+        scene.camera = PerspectiveCamera<C>(int2(d->camera.width, d->camera.height), c2w, d->camera.fov);
+        build_lights(*rs);
+        scene.sampler = LCGSampler<C>(); // core/nodes/scene.cpp:126
+        rs->accel.reset(new BVHAccelerator<C>());
+        scene.accel = rs->accel.get(); // core/nodes/scene.cpp:129-130
+        scene.commit();                // kernel/scene.cpp:64-81
+        return rs.release();
+    } catch (std::exception &e) {
+        g_err = e.what();
+        return nullptr;
+    }
+}
+
+void akref_scene_destroy(void *h) { delete (RefScene *)h; }
+
+uint64_t akref_n_lights(void *h) { return ((RefScene *)h)->lights.size(); }
+
+// Scene::intersect / Scene::occlude over a batch (kernel/scene.h:58-67), n_threads host threads.
+int akref_trace(void *h, const float *org_tmin, const float *dir_tmax, size_t n, int any_hit, akb_hit *out_hits,
+                int32_t *out_occ, int n_threads) {
+    AKR_IMPORT_TYPES()
+    auto *rs = (RefScene *)h;
+    const Scene<C> &scene = rs->scene;
+    if (n_threads <= 0)
+        n_threads = (int)std::thread::hardware_concurrency();
+    std::atomic<size_t> next{0};
+    const size_t chunk = 4096;
+    auto work = [&]() {
+        for (;;) {
+            size_t b = next.fetch_add(chunk);
+            if (b >= n)
+                break;
+            size_t e = std::min(n, b + chunk);
+            for (size_t i = b; i < e; i++) {
+                Ray3f ray(Float3(org_tmin[4 * i], org_tmin[4 * i + 1], org_tmin[4 * i + 2]),
+                          Float3(dir_tmax[4 * i], dir_tmax[4 * i + 1], dir_tmax[4 * i + 2]), org_tmin[4 * i + 3],
+                          dir_tmax[4 * i + 3]);
+                if (any_hit) {
+                    out_occ[i] = scene.occlude(ray) ? 1 : 0;
+                } else {
+                    Intersection<C> isct;
+                    akb_hit o;
+                    if (scene.intersect(ray, &isct)) {
+                        o.t = isct.t, o.u = isct.uv.x, o.v = isct.uv.y, o.prim_id = isct.prim_id, o.geom_id = isct.geom_id;
+                    } else {
+                        o.t = Constants<Float>::Inf(), o.u = 0, o.v = 0, o.prim_id = -1, o.geom_id = -1;
+                    }
+                    out_hits[i] = o;
+                }
+            }
+        }
+    };
+    std::vector<std::thread> ts;
+    for (int t = 1; t < n_threads; t++)
+        ts.emplace_back(work);
+    work();
+    for (auto &t : ts)
+        t.join();
+    return 0;
+}
+
+// Camera::generate_ray(u1,u2,raster) for a batch (kernel/camera.h:67-86). u1 is the lens sample (pinhole: unused).
+int akref_generate_rays(void *h, const int32_t *xy, const float *u2, size_t n, float *org_tmin, float *dir_tmax) {
+    AKR_IMPORT_TYPES()
+    auto *rs = (RefScene *)h;
+    for (size_t i = 0; i < n; i++) {
+        auto s = rs->scene.camera.generate_ray(float2(0.5f, 0.5f), float2(u2[2 * i], u2[2 * i + 1]),
+                                               int2(xy[2 * i], xy[2 * i + 1]));
+        org_tmin[4 * i] = s.ray.o.x, org_tmin[4 * i + 1] = s.ray.o.y, org_tmin[4 * i + 2] = s.ray.o.z;
+        org_tmin[4 * i + 3] = s.ray.tmin;
+        dir_tmax[4 * i] = s.ray.d.x, dir_tmax[4 * i + 1] = s.ray.d.y, dir_tmax[4 * i + 2] = s.ray.d.z;
+        dir_tmax[4 * i + 3] = s.ray.tmax;
+    }
+    return 0;
+}
+
+// Sampler known-answer helper: n draws of next1d() after set_sample_index(seed) (kernel/sampler.h:48-66),
+// and the (x,y) of the first next2d() on a fresh copy (pins the compiler-defined argument evaluation order).
+int akref_sampler_kat(int sampler_kind, uint64_t seed, int n, float *out, float *out_next2d) {
+    AKR_IMPORT_TYPES()
+    Sampler<C> s = sampler_kind == AKB_SAMPLER_PCG ? Sampler<C>(PCGSampler<C>()) : Sampler<C>(LCGSampler<C>());
+    s.set_sample_index(seed);
+    Sampler<C> s2 = s;
+    for (int i = 0; i < n; i++)
+        out[i] = s.next1d();
+    auto v = s2.next2d();
+    out_next2d[0] = v.x, out_next2d[1] = v.y;
+    return 0;
+}
+
+// The sampling loop of cpu::PathTracer::render (kernel/integrators/cpu/integrator.cpp:115-135) over the pixel
+// rectangle [x0,x1) x [y0,y1), writing (sum L, sum weight) per pixel as float4 into out_rgbw[(y*W+x)*4].
+// Pixels outside the rectangle are left untouched. counts (may be NULL): [0] samples.
+int akref_render(void *h, const akb_render_params *p, int x0, int y0, int x1, int y1, float *out_rgbw,
+                 int n_threads) {
+    AKR_IMPORT_TYPES()
+    auto *rs = (RefScene *)h;
+    if (p->integrator != AKB_INTEGRATOR_PATH || p->rr_start_depth != 0 || p->ray_clamp != 0.0f) {
+        g_err = "reference CPU path has no AO-through-this-entry/RR/clamp";
+        return 1;
+    }
+    Scene<C> &scene = rs->scene;
+    if (p->sampler == AKB_SAMPLER_PCG)
+        scene.sampler = PCGSampler<C>();
+    else
+        scene.sampler = LCGSampler<C>();
+    const int W = rs->width;
+    if (n_threads <= 0)
+        n_threads = (int)std::thread::hardware_concurrency();
+    const int spp = p->spp, max_depth = p->max_depth;
+    std::atomic<int> next_row{y0};
+    auto work = [&]() {
+        auto &camera = scene.camera;
+        auto sampler = scene.sampler;
+        for (;;) {
+            int y = next_row.fetch_add(1);
+            if (y >= y1)
+                break;
+            for (int x = x0; x < x1; x++) {
+                sampler.set_sample_index(x + y * W);
+                Spectrum sum(0);
+                Float weight = 0;
+                for (int s = 0; s < spp; s++) {
+                    sampler.start_next_sample();
+                    GenericPathTracer<C> pt;
+                    pt.depth = 0;
+                    pt.max_depth = max_depth;
+                    pt.sampler = sampler;
+                    pt.run_megakernel(scene, camera, int2(x, y));
+                    sampler = pt.sampler;
+                    weight += 1.0f;   // Tile::add_sample, core/film.h:66-70
+                    sum += pt.L;
+                }
+                float *o = out_rgbw + 4 * ((size_t)y * W + x);
+                o[0] = sum[0], o[1] = sum[1], o[2] = sum[2], o[3] = weight;
+            }
+        }
+    };
+    std::vector<std::thread> ts;
+    for (int t = 1; t < n_threads; t++)
+        ts.emplace_back(work);
+    work();
+    for (auto &t : ts)
+        t.join();
+    return 0;
+}
+
+} // extern "C"

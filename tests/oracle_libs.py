@@ -1,0 +1,137 @@
+"""ctypes loaders for the two CPU checkers (TEST INFRASTRUCTURE — never imported by the product package):
+
+  * `Oracle`   : oracle/libakari_oracle.so  — the plain-C restatement (oracle/akari_oracle.c)
+  * `Reference`: oracle/_ref/libakari_ref.so — the reference's own code behind oracle/ref_harness.cpp
+
+Both take the same `akb_scene_desc` the product library takes.
+"""
+import ctypes as C
+import importlib
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pkg = importlib.import_module("akarirender-1_b200")
+abi = pkg.abi
+
+ORACLE_SO = os.path.join(ROOT, "oracle", "libakari_oracle.so")
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libakari_ref.so")
+
+
+def build_oracle():
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "oracle"], check=True)
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class _Base:
+    prefix = None
+
+    def __init__(self, scene, lib, create_args=()):
+        self.lib = lib
+        self.desc, self._keep = scene.flatten()
+        self.width, self.height = scene.camera.resolution
+        create = getattr(lib, self.prefix + "_scene_create")
+        create.restype = C.c_void_p
+        self.h = create(C.byref(self.desc), *create_args)
+        if not self.h:
+            raise RuntimeError(f"{self.prefix}_scene_create failed")
+        self.h = C.c_void_p(self.h)
+
+    def close(self):
+        if self.h:
+            getattr(self.lib, self.prefix + "_scene_destroy")(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def n_lights(self):
+        f = getattr(self.lib, self.prefix + "_n_lights")
+        f.restype = C.c_uint64
+        return int(f(self.h))
+
+    def trace(self, org_tmin, dir_tmax, any_hit=False, threads=0):
+        org = np.ascontiguousarray(org_tmin, np.float32)
+        dr = np.ascontiguousarray(dir_tmax, np.float32)
+        n = org.shape[0]
+        hits = np.zeros(n, dtype=HIT_DTYPE)
+        occ = np.zeros(n, np.int32)
+        f = getattr(self.lib, self.prefix + "_trace")
+        rc = f(self.h, _ptr(org), _ptr(dr), C.c_size_t(n), C.c_int(int(any_hit)), _ptr(hits), _ptr(occ),
+               C.c_int(threads or os.cpu_count()))
+        assert rc == 0
+        return occ if any_hit else hits
+
+    def generate_rays(self, xy, u2):
+        xy = np.ascontiguousarray(xy, np.int32)
+        u2 = np.ascontiguousarray(u2, np.float32)
+        n = xy.shape[0]
+        org = np.zeros((n, 4), np.float32)
+        dr = np.zeros((n, 4), np.float32)
+        rc = getattr(self.lib, self.prefix + "_generate_rays")(self.h, _ptr(xy), _ptr(u2), C.c_size_t(n), _ptr(org),
+                                                                _ptr(dr))
+        assert rc == 0
+        return org, dr
+
+    def sampler_kat(self, kind, seed, n):
+        out = np.zeros(n, np.float32)
+        n2 = np.zeros(2, np.float32)
+        getattr(self.lib, self.prefix + "_sampler_kat")(C.c_int(kind), C.c_uint64(seed), C.c_int(n), _ptr(out), _ptr(n2))
+        return out, n2
+
+
+HIT_DTYPE = np.dtype([("t", np.float32), ("u", np.float32), ("v", np.float32), ("prim_id", np.int32),
+                      ("geom_id", np.int32)])
+
+
+class Oracle(_Base):
+    prefix = "akor"
+
+    def __init__(self, scene, brute_force=False):
+        if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(
+                os.path.join(ROOT, "oracle", "akari_oracle.c")):
+            build_oracle()
+        super().__init__(scene, C.CDLL(ORACLE_SO), (C.c_int(int(brute_force)),))
+
+    def render(self, params, rect=None, threads=0):
+        x0, y0, x1, y1 = rect or (0, 0, self.width, self.height)
+        film = np.zeros((self.height, self.width, 4), np.float32)
+        counts = (C.c_uint64 * 3)()
+        rc = self.lib.akor_render(self.h, C.byref(params), x0, y0, x1, y1, _ptr(film),
+                                  C.c_int(threads or os.cpu_count()), counts)
+        assert rc == 0
+        self.counts = tuple(int(c) for c in counts)
+        return film
+
+    def film_to_srgb8(self, film):
+        h, w = film.shape[:2]
+        out = np.zeros((h, w, 3), np.uint8)
+        self.lib.akor_film_to_srgb8(_ptr(np.ascontiguousarray(film, np.float32)), w, h, _ptr(out))
+        return out
+
+
+class Reference(_Base):
+    prefix = "akref"
+
+    def __init__(self, scene):
+        super().__init__(scene, C.CDLL(REF_SO))
+
+    def render(self, params, rect=None, threads=0):
+        x0, y0, x1, y1 = rect or (0, 0, self.width, self.height)
+        film = np.zeros((self.height, self.width, 4), np.float32)
+        rc = self.lib.akref_render(self.h, C.byref(params), x0, y0, x1, y1, _ptr(film),
+                                   C.c_int(threads or os.cpu_count()))
+        assert rc == 0
+        return film
