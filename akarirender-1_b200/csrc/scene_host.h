@@ -1,0 +1,64 @@
+// scene_host.h — host-side flattening of an akb_scene_desc into the arrays the kernels read.
+//
+// Replaces SceneNode::compile (core/nodes/scene.cpp:43-95: mesh views, AreaLight list, power Distribution1D),
+// PerspectiveCamera::preprocess (kernel/camera.h:45-59) and `scene.accel = BVHAccelerator; scene.commit()`
+// (core/nodes/scene.cpp:127-135, kernel/scene.cpp:64-81). Pure C++ (no CUDA): api.cu uploads the result to HBM.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "../../include/akari_b200.h"
+#include "bvh8.h"
+#include "shade.h"
+
+namespace akb {
+
+struct f4 {
+    float x, y, z, w;
+};
+
+struct HostScene {
+    uint64_t n_tris = 0;
+    std::vector<uint64_t> geom_offset; // n_meshes + 1
+    Bvh8 bvh;
+    std::vector<f4> tris;    // 3 per triangle, leaf order
+    std::vector<f4> shading; // 6 per triangle, flat order
+    std::vector<akb_material> mats;
+    std::vector<f4> lights; // 4 per light
+    std::vector<float> light_func, light_cdf;
+    float light_func_int = 0;
+    CameraDev cam;
+};
+
+// Returns AKB_OK or AKB_INVALID_ARG (+ message).
+akb_status flatten_scene(const akb_scene_desc *desc, int n_threads, HostScene *out, std::string *err);
+
+// Interleaved-tile pixel ownership: slot -> pixel. Slots are grouped per owned tile, Morton order
+// inside the tile so that one warp covers an 8x4 pixel block.
+struct SlotMap {
+    int width, height, tile, tiles_x, tiles_y, rank, world;
+    int n_owned_tiles;
+    AKB_HD int n_slots() const { return n_owned_tiles * tile * tile; }
+};
+SlotMap make_slot_map(int width, int height, int tile, int rank, int world);
+
+AKB_HD uint32_t morton_compact(uint32_t v) { // even bits of v -> low half
+    v &= 0x55555555u;
+    v = (v | (v >> 1)) & 0x33333333u;
+    v = (v | (v >> 2)) & 0x0F0F0F0Fu;
+    v = (v | (v >> 4)) & 0x00FF00FFu;
+    v = (v | (v >> 8)) & 0x0000FFFFu;
+    return v;
+}
+// false when the slot falls outside the image (edge tiles)
+AKB_HD bool slot_to_pixel(const SlotMap &m, int slot, int &x, int &y) {
+    const int tt = m.tile * m.tile;
+    const int lt = slot / tt, in = slot - lt * tt;
+    const int t = lt * m.world + m.rank;
+    const int ty = t / m.tiles_x, tx = t - ty * m.tiles_x;
+    x = tx * m.tile + (int)morton_compact((uint32_t)in);
+    y = ty * m.tile + (int)morton_compact((uint32_t)in >> 1);
+    return x < m.width && y < m.height;
+}
+
+} // namespace akb

@@ -1,0 +1,187 @@
+// traverse.h — closest-hit / any-hit traversal of the compressed 8-wide BVH (bvh8.h) for ONE ray.
+//
+// Replaces TBVHAccelerator::intersect / occlude (kernel/bvh-accelerator.h:488-547), intersectAABB (:89-103),
+// intersect_leaf (:476-486), BVHIntersector (:651-664) and MeshInstance::intersect (kernel/instance.h:42-80).
+//
+// Result contract (what makes it a drop-in): the nearest t over ALL triangles that pass the reference's
+// Moeller-Trumbore test, evaluated with the reference's exact fp32 operation order (no FMA, IEEE divide), with
+// the reference's constants and comparisons (|a| < 1e-6 reject, inclusive u in [0,1], u+v <= 1, exclusive
+// tmin < t < tmax, strict t < best). Among candidates with bit-identical t the lowest flat triangle id wins
+// (the reference resolves such exact ties by its own BVH's visit order, which no other tree can reproduce).
+// Box culling is conservative: quantised child boxes are supersets of padded triangle boxes, NaNs from 0*inf
+// drop out of fminf/fmaxf, so the box test only ever skips work, never a hit.
+//
+// The code is AKB_HD so that tests/hostcheck can run the very same traversal on the CPU against the oracle
+// (test infrastructure only; the library exports no CPU path).
+#pragma once
+#include "vecmath.h"
+
+namespace akb {
+
+#ifdef __CUDA_ARCH__
+#define AKB_LD4(p) __ldg(p)
+__device__ __forceinline__ uint32_t akb_f2u(float f) { return __float_as_uint(f); }
+__device__ __forceinline__ float akb_u2f(uint32_t u) { return __uint_as_float(u); }
+__device__ __forceinline__ int akb_bfind(uint32_t x) { return 31 - __clz((int)x); }
+__device__ __forceinline__ int akb_popc(uint32_t x) { return __popc(x); }
+__device__ __forceinline__ uint32_t akb_sext_s8x4(uint32_t x) { // per byte: 0xFF if bit 7 set else 0x00
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(0u), "r"(0xba98u));
+    return r;
+}
+#else
+#define AKB_LD4(p) (*(p))
+#ifndef __CUDACC__
+struct float4 {
+    float x, y, z, w;
+};
+struct uint2 {
+    uint32_t x, y;
+};
+#endif
+inline uint32_t akb_f2u(float f) {
+    uint32_t u;
+    __builtin_memcpy(&u, &f, 4);
+    return u;
+}
+inline float akb_u2f(uint32_t u) {
+    float f;
+    __builtin_memcpy(&f, &u, 4);
+    return f;
+}
+inline int akb_bfind(uint32_t x) { return 31 - __builtin_clz(x); }
+inline int akb_popc(uint32_t x) { return __builtin_popcount(x); }
+inline uint32_t akb_sext_s8x4(uint32_t x) {
+    uint32_t r = 0;
+    for (int i = 0; i < 4; i++)
+        if (x & (0x80u << (8 * i))) r |= 0xFFu << (8 * i);
+    return r;
+}
+#endif
+
+struct RayHit {
+    float t, u, v;
+    int tri; // flat triangle id, -1 = miss
+    int mat; // scene material index of the hit triangle (from the leaf record)
+};
+
+// MeshInstance::intersect, kernel/instance.h:42-80, on a leaf-order triangle record
+// (r0 = v0|flat id, r1 = e1|material, r2 = e2|-). e1 = v1 - v0 and e2 = v2 - v0 are the reference's own first two
+// subtractions, done once at scene build in the same fp32 arithmetic (bit-identical to doing them per ray).
+// Returns t or a negative sentinel; u,v written on success.
+AKB_HD bool mt_test(v3 o, v3 d, float tmin, float tmax, const float4 &r0, const float4 &r1, const float4 &r2,
+                    float &t_out, float &u_out, float &v_out) {
+    v3 v0 = mk3(r0.x, r0.y, r0.z), e1 = mk3(r1.x, r1.y, r1.z), e2 = mk3(r2.x, r2.y, r2.z);
+    v3 h = cross3(d, e2);
+    float a = dot3(e1, h);
+    if (a > -1e-6f && a < 1e-6f) return false;
+    float f = 1.0f / a;
+    v3 s = sub3(o, v0);
+    float u = f * dot3(s, h);
+    if (u < 0.0f || u > 1.0f) return false;
+    v3 q = cross3(s, e1);
+    float v = f * dot3(d, q);
+    if (v < 0.0f || u + v > 1.0f) return false;
+    float t = f * dot3(e2, q);
+    if (t > tmin && t < tmax) {
+        t_out = t, u_out = u, v_out = v;
+        return true;
+    }
+    return false;
+}
+
+constexpr int kStackSize = 32;
+
+template <bool ANY>
+AKB_HD bool traverse8(const float4 *__restrict__ nodes, const float4 *__restrict__ tris, v3 o, v3 d, float tmin,
+                      float tmax, RayHit &hit) {
+    const float ooeps = 8.271806125530277e-25f; // 2^-80: keeps 1/d finite; far below any geometric scale
+    const float idx = 1.0f / (fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+    const float idy = 1.0f / (fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+    const float idz = 1.0f / (fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+    const uint32_t oct_inv = 7u - ((idx < 0 ? 1u : 0u) | (idy < 0 ? 2u : 0u) | (idz < 0 ? 4u : 0u));
+    const uint32_t oct_inv4 = oct_inv * 0x01010101u;
+
+    uint2 stack[kStackSize];
+    int sp = 0;
+    uint2 ng;
+    ng.x = 0, ng.y = 0x80000000u;
+    float tbest = tmax;
+    hit.tri = -1, hit.t = INFINITY, hit.u = 0.f, hit.v = 0.f, hit.mat = -1;
+
+    for (;;) {
+        if (ng.y > 0x00FFFFFFu) {
+            const uint32_t imask = ng.y & 0xFFu;
+            const int bit = akb_bfind(ng.y);
+            ng.y &= ~(1u << bit);
+            if (ng.y > 0x00FFFFFFu && sp < kStackSize) stack[sp++] = ng;
+            const uint32_t slot = (uint32_t)(bit - 24) ^ oct_inv;
+            const uint32_t rel = (uint32_t)akb_popc(imask & ~(0xFFFFFFFFu << slot));
+            const float4 *np = nodes + 5 * (size_t)(ng.x + rel);
+            const float4 n0 = AKB_LD4(np), n1 = AKB_LD4(np + 1), n2 = AKB_LD4(np + 2), n3 = AKB_LD4(np + 3),
+                         n4 = AKB_LD4(np + 4);
+            const uint32_t ew = akb_f2u(n0.w);
+            const float adjx = akb_u2f((ew & 0xFFu) << 23) * idx;
+            const float adjy = akb_u2f(((ew >> 8) & 0xFFu) << 23) * idy;
+            const float adjz = akb_u2f(((ew >> 16) & 0xFFu) << 23) * idz;
+            const float orgx = (n0.x - o.x) * idx, orgy = (n0.y - o.y) * idy, orgz = (n0.z - o.z) * idz;
+            ng.x = akb_f2u(n1.x);
+            const uint32_t tri_base = akb_f2u(n1.y);
+            uint32_t hitmask = 0;
+#pragma unroll
+            for (int half = 0; half < 2; half++) {
+                const uint32_t meta4 = akb_f2u(half ? n1.w : n1.z);
+                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                const uint32_t inner_mask4 = akb_sext_s8x4(is_inner4 << 3);
+                const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1F1F1F1Fu;
+                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+                const uint32_t qlox = akb_f2u(half ? n2.y : n2.x), qloy = akb_f2u(half ? n2.w : n2.z);
+                const uint32_t qloz = akb_f2u(half ? n3.y : n3.x), qhix = akb_f2u(half ? n3.w : n3.z);
+                const uint32_t qhiy = akb_f2u(half ? n4.y : n4.x), qhiz = akb_f2u(half ? n4.w : n4.z);
+                const uint32_t nx = idx < 0 ? qhix : qlox, fx = idx < 0 ? qlox : qhix;
+                const uint32_t ny = idy < 0 ? qhiy : qloy, fy = idy < 0 ? qloy : qhiy;
+                const uint32_t nz = idz < 0 ? qhiz : qloz, fz = idz < 0 ? qloz : qhiz;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int sh = 8 * j;
+                    const float tlx = fmaf((float)((nx >> sh) & 0xFFu), adjx, orgx);
+                    const float tly = fmaf((float)((ny >> sh) & 0xFFu), adjy, orgy);
+                    const float tlz = fmaf((float)((nz >> sh) & 0xFFu), adjz, orgz);
+                    const float thx = fmaf((float)((fx >> sh) & 0xFFu), adjx, orgx);
+                    const float thy = fmaf((float)((fy >> sh) & 0xFFu), adjy, orgy);
+                    const float thz = fmaf((float)((fz >> sh) & 0xFFu), adjz, orgz);
+                    const float cmin = fmaxf(fmaxf(tlx, tly), fmaxf(tlz, tmin));
+                    const float cmax = fminf(fminf(thx, thy), fminf(thz, tbest));
+                    if (cmin <= cmax) hitmask |= ((child_bits4 >> sh) & 0xFFu) << ((bit_index4 >> sh) & 0xFFu);
+                }
+            }
+            ng.y = (hitmask & 0xFF000000u) | (ew >> 24);
+            uint32_t tmask = hitmask & 0x00FFFFFFu;
+            while (tmask) {
+                const int j = akb_bfind(tmask);
+                tmask &= ~(1u << j);
+                const float4 *tp = tris + 3 * (size_t)(tri_base + (uint32_t)j);
+                const float4 r0 = AKB_LD4(tp), r1 = AKB_LD4(tp + 1), r2 = AKB_LD4(tp + 2);
+                float t, u, v;
+                if (ANY) {
+                    if (mt_test(o, d, tmin, tmax, r0, r1, r2, t, u, v)) return true;
+                } else {
+                    // bound = +inf so that an exact tie with the current best still reaches the id comparison
+                    if (mt_test(o, d, tmin, tmax, r0, r1, r2, t, u, v)) {
+                        const int id = (int)akb_f2u(r0.w);
+                        if (t < tbest || (t == tbest && hit.tri >= 0 && id < hit.tri)) {
+                            tbest = t;
+                            hit.t = t, hit.u = u, hit.v = v, hit.tri = id, hit.mat = (int)akb_f2u(r1.w);
+                        }
+                    }
+                }
+            }
+        } else {
+            if (sp == 0) break;
+            ng = stack[--sp];
+        }
+    }
+    return hit.tri >= 0;
+}
+
+} // namespace akb

@@ -135,3 +135,39 @@ class Reference(_Base):
                                    C.c_int(threads or os.cpu_count()))
         assert rc == 0
         return film
+
+
+HOSTCHECK_DIR = os.path.join(ROOT, "tests", "hostcheck")
+HOSTCHECK_SO = os.path.join(HOSTCHECK_DIR, "libakari_hostcheck.so")
+CSRC = os.path.join(ROOT, "akarirender-1_b200", "csrc")
+
+
+def build_hostcheck():
+    srcs = [os.path.join(HOSTCHECK_DIR, "hostcheck.cpp"), os.path.join(CSRC, "scene_host.cpp"),
+            os.path.join(CSRC, "bvh8.cpp")]
+    deps = srcs + [os.path.join(CSRC, f) for f in ("scene_host.h", "bvh8.h", "shade.h", "traverse.h", "vecmath.h")]
+    if os.path.exists(HOSTCHECK_SO) and all(os.path.getmtime(HOSTCHECK_SO) >= os.path.getmtime(d) for d in deps):
+        return
+    subprocess.run(["g++", "-std=c++17", "-O2", "-mavx2", "-mfma", "-ffp-contract=off", "-fPIC", "-shared", "-pthread",
+                    "-o", HOSTCHECK_SO] + srcs, check=True)
+
+
+class HostCheck(_Base):
+    """The product's host-side scene build + the kernels' AKB_HD device functions compiled for the CPU
+    (tests/hostcheck/hostcheck.cpp). Test infrastructure: checks host logic without a GPU."""
+    prefix = "hc"
+
+    def __init__(self, scene, threads=0):
+        build_hostcheck()
+        super().__init__(scene, C.CDLL(HOSTCHECK_SO), (C.c_int(threads or os.cpu_count()),))
+        self.lib.hc_info.restype = C.c_uint64
+
+    def info(self):
+        keys = ["n_triangles", "n_bvh_nodes", "bvh_bytes", "n_lights", "triangle_bytes", "bvh_depth", "build_us"]
+        return {k: int(self.lib.hc_info(self.h, i)) for i, k in enumerate(keys)}
+
+    def render(self, params, threads=0):
+        film = np.zeros((self.height, self.width, 4), np.float32)
+        rc = self.lib.hc_render(self.h, C.byref(params), _ptr(film), C.c_int(threads or os.cpu_count()))
+        assert rc == 0
+        return film
