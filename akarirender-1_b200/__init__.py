@@ -13,6 +13,8 @@ import numpy as np
 
 from . import abi, nodes, scenes  # noqa: F401
 
+# `distributed` (torch.distributed plumbing for the multi-GPU frame split) is imported lazily: it needs torch.
+
 HIT_DTYPE = np.dtype([("t", np.float32), ("u", np.float32), ("v", np.float32), ("prim_id", np.int32),
                       ("geom_id", np.int32)])
 

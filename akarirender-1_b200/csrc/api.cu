@@ -1,0 +1,411 @@
+// api.cu — the C ABI of libakari_b200.so (include/akari_b200.h): device/scene lifecycle, HBM residency, the render
+// driver (wavefront bounce loop or megakernel) and the batch ray-query entry points. No CPU fallback: every compute
+// entry fails with AKB_NO_DEVICE / AKB_CUDA_ERROR when the GPU path is unavailable.
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+
+using namespace akb;
+
+namespace {
+
+thread_local std::string g_err;
+int g_device = -1;
+int g_n_sms = 0;
+bool g_profile_stages = false;
+
+akb_status set_err(akb_status st, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return st;
+}
+
+#define CU(call)                                                                                                       \
+    do {                                                                                                               \
+        cudaError_t e_ = (call);                                                                                       \
+        if (e_ != cudaSuccess)                                                                                         \
+            return set_err(e_ == cudaErrorMemoryAllocation ? AKB_OOM : AKB_CUDA_ERROR, "%s: %s (%s:%d)", #call,        \
+                           cudaGetErrorString(e_), __FILE__, __LINE__);                                                \
+    } while (0)
+
+} // namespace
+
+struct akb_scene {
+    SceneDev dev;
+    std::vector<void *> allocs;
+    uint64_t n_tris = 0, n_nodes = 0, bvh_bytes = 0, n_lights = 0, tri_bytes = 0, bvh_depth = 0, build_us = 0;
+    int width = 0, height = 0;
+    // render workspace (lazily sized)
+    Workspace ws;
+    std::vector<void *> ws_allocs;
+    int ws_slots = 0;
+    Counters *d_ctr = nullptr, *h_ctr = nullptr;
+    float4 *d_film = nullptr;
+    size_t d_film_px = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+    void free_ws() {
+        for (void *p : ws_allocs) cudaFree(p);
+        ws_allocs.clear();
+        ws_slots = 0;
+    }
+    ~akb_scene() {
+        free_ws();
+        for (void *p : allocs) cudaFree(p);
+        if (d_ctr) cudaFree(d_ctr);
+        if (h_ctr) cudaFreeHost(h_ctr);
+        if (d_film) cudaFree(d_film);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+    }
+};
+
+namespace {
+
+template <class T> akb_status upload(akb_scene *sc, const T *src, size_t n, const T **dst) {
+    void *p = nullptr;
+    size_t bytes = std::max<size_t>(n * sizeof(T), 16);
+    CU(cudaMalloc(&p, bytes));
+    sc->allocs.push_back(p);
+    if (n) CU(cudaMemcpy(p, src, n * sizeof(T), cudaMemcpyHostToDevice));
+    *dst = (const T *)p;
+    return AKB_OK;
+}
+
+template <class T> akb_status ws_alloc(akb_scene *sc, size_t n, T **dst) {
+    void *p = nullptr;
+    CU(cudaMalloc(&p, std::max<size_t>(n * sizeof(T), 16)));
+    sc->ws_allocs.push_back(p);
+    *dst = (T *)p;
+    return AKB_OK;
+}
+
+akb_status ensure_workspace(akb_scene *sc, int n_slots) {
+    if (sc->ws_slots >= n_slots && sc->ws_slots > 0) {
+        sc->ws.n_slots = n_slots;
+        return AKB_OK;
+    }
+    sc->free_ws();
+    Workspace &w = sc->ws;
+    const size_t n = (size_t)std::max(n_slots, 32);
+    akb_status st;
+#define WS(field, type)                                                                                                \
+    if ((st = ws_alloc<type>(sc, n, &w.field)) != AKB_OK) return st;
+    WS(ray_o, float4) WS(ray_d, float4) WS(hit, float4) WS(beta, float4) WS(L, float4) WS(rng, unsigned long long)
+    WS(sh_o, float4) WS(sh_d, float4) WS(sh_c, float4) WS(acc, float4)
+    for (int b = 0; b < 2; b++) {
+        WS(q_ext[b], uint32_t) WS(q_sh[b], uint32_t)
+        for (int k = 0; k < kNumKeys; k++) { WS(q_shade[b][k], uint32_t) }
+    }
+#undef WS
+    w.ctr = sc->d_ctr;
+    w.n_slots = n_slots;
+    sc->ws_slots = n_slots;
+    return AKB_OK;
+}
+
+akb_status check_ready(const char *who) {
+    if (g_device < 0) return set_err(AKB_NO_DEVICE, "%s: akb_init() has not succeeded (no CUDA device bound; there is no CPU fallback)", who);
+    return AKB_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *akb_last_error(void) { return g_err.c_str(); }
+
+int akb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+akb_status akb_init(int device_index) {
+    int n = akb_device_count();
+    if (n <= 0) return set_err(AKB_NO_DEVICE, "akb_init: no CUDA device visible (this backend has no CPU fallback)");
+    if (device_index < 0 || device_index >= n) return set_err(AKB_INVALID_ARG, "akb_init: device %d out of range [0,%d)", device_index, n);
+    CU(cudaSetDevice(device_index));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device_index));
+    if (prop.major < 10)
+        return set_err(AKB_NO_DEVICE, "akb_init: device %d is sm_%d%d; this library carries sm_100a code only", device_index, prop.major, prop.minor);
+    g_n_sms = prop.multiProcessorCount;
+    // arithmetic self-test: the parity contract needs un-contracted fp32 (see vecmath.h)
+    int *d_res = nullptr, h_res = 0;
+    CU(cudaMalloc(&d_res, sizeof(int)));
+    cudaError_t e = launch_selftest(d_res, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(&h_res, d_res, sizeof(int), cudaMemcpyDeviceToHost);
+    cudaFree(d_res);
+    if (e != cudaSuccess) return set_err(AKB_CUDA_ERROR, "akb_init: self-test launch failed: %s", cudaGetErrorString(e));
+    if (h_res != 1) return set_err(AKB_CUDA_ERROR, "akb_init: kernels were built with FMA contraction; rebuild with -fmad=false");
+    const char *pf = getenv("AKB_PROFILE_STAGES");
+    g_profile_stages = pf && pf[0] == '1';
+    g_device = device_index;
+    return AKB_OK;
+}
+
+akb_status akb_shutdown(void) {
+    if (g_device >= 0) cudaDeviceSynchronize();
+    g_device = -1;
+    return AKB_OK;
+}
+
+akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
+    if (!out_scene) return set_err(AKB_INVALID_ARG, "akb_scene_create: out_scene == NULL");
+    *out_scene = nullptr;
+    akb_status st = check_ready("akb_scene_create");
+    if (st != AKB_OK) return st;
+    HostScene hs;
+    std::string err;
+    st = flatten_scene(desc, 0, &hs, &err);
+    if (st != AKB_OK) return set_err(st, "%s", err.c_str());
+    akb_scene *sc = new akb_scene();
+    SceneDev &S = sc->dev;
+    memset(&S, 0, sizeof S);
+    st = upload(sc, (const float4 *)hs.bvh.nodes.data(), hs.bvh.nodes.size() * 5, &S.nodes);
+    if (st == AKB_OK) st = upload(sc, (const float4 *)hs.tris.data(), hs.tris.size(), &S.tris);
+    if (st == AKB_OK) st = upload(sc, (const float4 *)hs.shading.data(), hs.shading.size(), &S.shading);
+    if (st == AKB_OK) st = upload(sc, hs.mats.data(), hs.mats.size(), &S.mats);
+    if (st == AKB_OK) st = upload(sc, (const float4 *)hs.lights.data(), hs.lights.size(), &S.lights);
+    if (st == AKB_OK) st = upload(sc, hs.light_cdf.data(), hs.light_cdf.size(), &S.light_cdf);
+    if (st == AKB_OK) st = upload(sc, hs.light_func.data(), hs.light_func.size(), &S.light_func);
+    if (st == AKB_OK) {
+        cudaError_t e = cudaMalloc((void **)&sc->d_ctr, sizeof(Counters));
+        if (e == cudaSuccess) e = cudaMallocHost((void **)&sc->h_ctr, sizeof(Counters));
+        if (e == cudaSuccess) e = cudaEventCreate(&sc->ev0);
+        if (e == cudaSuccess) e = cudaEventCreate(&sc->ev1);
+        if (e != cudaSuccess) st = set_err(AKB_CUDA_ERROR, "akb_scene_create: %s", cudaGetErrorString(e));
+    }
+    if (st != AKB_OK) {
+        delete sc;
+        return st;
+    }
+    S.light_func_int = hs.light_func_int;
+    S.n_lights = (int)hs.light_func.size();
+    S.n_mats = (int)hs.mats.size();
+    S.cam = hs.cam;
+    sc->n_tris = hs.n_tris, sc->n_nodes = hs.bvh.nodes.size(), sc->bvh_bytes = hs.bvh.nodes.size() * sizeof(Node8);
+    sc->n_lights = hs.light_func.size(), sc->tri_bytes = hs.tris.size() * sizeof(f4);
+    sc->bvh_depth = (uint64_t)hs.bvh.depth, sc->build_us = (uint64_t)(hs.bvh.build_seconds * 1e6);
+    sc->width = hs.cam.width, sc->height = hs.cam.height;
+    *out_scene = sc;
+    return AKB_OK;
+}
+
+akb_status akb_scene_destroy(akb_scene *scene) {
+    if (!scene) return AKB_OK;
+    if (g_device >= 0) cudaDeviceSynchronize();
+    delete scene;
+    return AKB_OK;
+}
+
+uint64_t akb_scene_info(const akb_scene *sc, int what) {
+    if (!sc) return 0;
+    switch (what) {
+    case 0: return sc->n_tris;
+    case 1: return sc->n_nodes;
+    case 2: return sc->bvh_bytes;
+    case 3: return sc->n_lights;
+    case 4: return sc->tri_bytes;
+    case 5: return sc->bvh_depth;
+    case 6: return sc->build_us;
+    }
+    return 0;
+}
+
+akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d_out_rgbw, void *cuda_stream,
+                             akb_render_stats *stats) {
+    akb_status st = check_ready("akb_render_device");
+    if (st != AKB_OK) return st;
+    if (!sc || !p || !d_out_rgbw) return set_err(AKB_INVALID_ARG, "akb_render_device: null argument");
+    if (p->integrator != AKB_INTEGRATOR_PATH) return set_err(AKB_INVALID_ARG, "akb_render_device: only the Path integrator is implemented");
+    if (p->spp < 0 || p->max_depth < 0) return set_err(AKB_INVALID_ARG, "akb_render_device: negative spp/max_depth");
+    if (p->sampler != AKB_SAMPLER_LCG && p->sampler != AKB_SAMPLER_PCG) return set_err(AKB_INVALID_ARG, "akb_render_device: bad sampler");
+    const int world = p->world_size > 0 ? p->world_size : 1;
+    if (p->rank < 0 || p->rank >= world) return set_err(AKB_INVALID_ARG, "akb_render_device: rank %d outside world_size %d", p->rank, world);
+    const int tile = p->tile_size > 0 ? p->tile_size : 32;
+    if ((tile & (tile - 1)) != 0 || tile < 8 || tile > 1024) return set_err(AKB_INVALID_ARG, "akb_render_device: tile_size must be a power of two in [8,1024]");
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    RenderConfig rc;
+    rc.spp = p->spp, rc.max_depth = p->max_depth, rc.rr_start = p->rr_start_depth, rc.sampler = p->sampler;
+    rc.sort_materials = p->sort_materials, rc.ray_clamp = p->ray_clamp;
+    rc.map = make_slot_map(sc->width, sc->height, tile, p->rank, world);
+    const size_t n_px = (size_t)sc->width * sc->height;
+    uint64_t launches = 0;
+    std::vector<cudaEvent_t> evs;
+    CU(cudaMemsetAsync(d_out_rgbw, 0, n_px * sizeof(float4), stream));
+    CU(cudaMemsetAsync(sc->d_ctr, 0, sizeof(Counters), stream));
+    CU(cudaEventRecord(sc->ev0, stream));
+    if (p->mode == AKB_MODE_MEGAKERNEL) {
+        CU(launch_megakernel(sc->dev, rc, (float4 *)d_out_rgbw, sc->d_ctr, stream));
+        launches = 1;
+    } else {
+        st = ensure_workspace(sc, rc.map.n_slots());
+        if (st != AKB_OK) return st;
+        CU(launch_wf_init(sc->dev, rc, sc->ws, g_n_sms, stream));
+        launches++;
+        const long max_it = (long)rc.spp * (rc.max_depth + 2) + 2;
+        const int check_every = 4;
+        auto mark = [&]() {
+            if (!g_profile_stages) return cudaSuccess;
+            cudaEvent_t e;
+            cudaError_t r = cudaEventCreate(&e);
+            if (r != cudaSuccess) return r;
+            evs.push_back(e);
+            return cudaEventRecord(e, stream);
+        };
+        CU(mark());
+        for (long it = 0; it < max_it && rc.map.n_slots() > 0 && rc.spp > 0; it++) {
+            const int b = (int)(it & 1);
+            CU(launch_wf_trace(sc->dev, rc, sc->ws, b, g_n_sms, stream));
+            CU(mark());
+            CU(launch_wf_shade(sc->dev, rc, sc->ws, b, g_n_sms, stream));
+            CU(mark());
+            launches += 2;
+            if ((it % check_every) == check_every - 1) {
+                CU(cudaMemcpyAsync(sc->h_ctr, sc->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+                CU(cudaStreamSynchronize(stream));
+                if (sc->h_ctr->n_ext[b ^ 1] == 0 && sc->h_ctr->n_sh[b ^ 1] == 0) break;
+            }
+        }
+        CU(launch_wf_resolve(rc, sc->ws, (float4 *)d_out_rgbw, stream));
+        launches++;
+    }
+    CU(cudaEventRecord(sc->ev1, stream));
+    CU(cudaMemcpyAsync(sc->h_ctr, sc->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+    CU(cudaStreamSynchronize(stream));
+    if (stats) {
+        memset(stats, 0, sizeof *stats);
+        stats->n_samples = sc->h_ctr->stat_samples;
+        stats->n_closest_rays = sc->h_ctr->stat_closest - sc->h_ctr->stat_skipped;
+        stats->n_shadow_rays = sc->h_ctr->stat_shadow;
+        stats->n_kernel_launches = launches;
+        CU(cudaEventElapsedTime(&stats->ms_total, sc->ev0, sc->ev1));
+        if (evs.size() >= 3) {
+            for (size_t i = 1; i + 1 < evs.size(); i += 2) {
+                float a = 0, b2 = 0;
+                cudaEventElapsedTime(&a, evs[i - 1], evs[i]);
+                cudaEventElapsedTime(&b2, evs[i], evs[i + 1]);
+                stats->ms_extend += a, stats->ms_shade += b2;
+            }
+        }
+    }
+    for (cudaEvent_t e : evs) cudaEventDestroy(e);
+    return AKB_OK;
+}
+
+akb_status akb_render(akb_scene *sc, const akb_render_params *p, float *out_rgbw, akb_render_stats *stats) {
+    akb_status st = check_ready("akb_render");
+    if (st != AKB_OK) return st;
+    if (!sc || !p || !out_rgbw) return set_err(AKB_INVALID_ARG, "akb_render: null argument");
+    const size_t n_px = (size_t)sc->width * sc->height;
+    if (sc->d_film_px < n_px) {
+        if (sc->d_film) cudaFree(sc->d_film);
+        sc->d_film = nullptr, sc->d_film_px = 0;
+        CU(cudaMalloc((void **)&sc->d_film, n_px * sizeof(float4)));
+        sc->d_film_px = n_px;
+    }
+    st = akb_render_device(sc, p, (float *)sc->d_film, nullptr, stats);
+    if (st != AKB_OK) return st;
+    CU(cudaMemcpy(out_rgbw, sc->d_film, n_px * sizeof(float4), cudaMemcpyDeviceToHost));
+    return AKB_OK;
+}
+
+akb_status akb_trace_device(akb_scene *sc, const float *d_org, const float *d_dir, size_t n, int any_hit, akb_hit *d_hits,
+                            int32_t *d_occ, void *cuda_stream, float *ms_kernel) {
+    akb_status st = check_ready("akb_trace_device");
+    if (st != AKB_OK) return st;
+    if (!sc || (n && (!d_org || !d_dir)) || (n && !any_hit && !d_hits) || (n && any_hit && !d_occ))
+        return set_err(AKB_INVALID_ARG, "akb_trace_device: null argument");
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    if (ms_kernel) CU(cudaEventRecord(sc->ev0, stream));
+    CU(launch_trace_batch(sc->dev, (const float4 *)d_org, (const float4 *)d_dir, n, any_hit, d_hits, d_occ, g_n_sms, stream));
+    if (ms_kernel) CU(cudaEventRecord(sc->ev1, stream));
+    CU(cudaStreamSynchronize(stream));
+    if (ms_kernel) CU(cudaEventElapsedTime(ms_kernel, sc->ev0, sc->ev1));
+    return AKB_OK;
+}
+
+akb_status akb_trace(akb_scene *sc, const float *org, const float *dir, size_t n, int any_hit, akb_hit *out_hits,
+                     int32_t *out_occ) {
+    akb_status st = check_ready("akb_trace");
+    if (st != AKB_OK) return st;
+    if (!sc || (n && (!org || !dir)) || (n && !any_hit && !out_hits) || (n && any_hit && !out_occ))
+        return set_err(AKB_INVALID_ARG, "akb_trace: null argument");
+    const size_t chunk = std::min<size_t>(n, (size_t)1 << 24);
+    if (n == 0) return AKB_OK;
+    float4 *d_o = nullptr, *d_d = nullptr;
+    void *d_out = nullptr;
+    const size_t out_elt = any_hit ? sizeof(int32_t) : sizeof(akb_hit);
+    cudaError_t e = cudaMalloc((void **)&d_o, chunk * sizeof(float4));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&d_d, chunk * sizeof(float4));
+    if (e == cudaSuccess) e = cudaMalloc(&d_out, chunk * out_elt);
+    for (size_t off = 0; off < n && e == cudaSuccess; off += chunk) {
+        const size_t m = std::min(chunk, n - off);
+        e = cudaMemcpy(d_o, org + 4 * off, m * sizeof(float4), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(d_d, dir + 4 * off, m * sizeof(float4), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = launch_trace_batch(sc->dev, d_o, d_d, m, any_hit, (akb_hit *)d_out, (int32_t *)d_out, g_n_sms, 0);
+        if (e == cudaSuccess)
+            e = cudaMemcpy(any_hit ? (void *)(out_occ + off) : (void *)(out_hits + off), d_out, m * out_elt, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(d_o), cudaFree(d_d), cudaFree(d_out);
+    if (e != cudaSuccess)
+        return set_err(e == cudaErrorMemoryAllocation ? AKB_OOM : AKB_CUDA_ERROR, "akb_trace: %s", cudaGetErrorString(e));
+    return AKB_OK;
+}
+
+akb_status akb_generate_rays(akb_scene *sc, const int32_t *xy, const float *u2, size_t n, float *org, float *dir) {
+    akb_status st = check_ready("akb_generate_rays");
+    if (st != AKB_OK) return st;
+    if (!sc || (n && (!xy || !u2 || !org || !dir))) return set_err(AKB_INVALID_ARG, "akb_generate_rays: null argument");
+    if (n == 0) return AKB_OK;
+    int32_t *d_xy = nullptr;
+    float *d_u = nullptr;
+    float4 *d_o = nullptr, *d_d = nullptr;
+    cudaError_t e = cudaMalloc((void **)&d_xy, n * 8);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&d_u, n * 8);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&d_o, n * 16);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&d_d, n * 16);
+    if (e == cudaSuccess) e = cudaMemcpy(d_xy, xy, n * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_u, u2, n * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = launch_generate_rays(sc->dev, d_xy, d_u, n, d_o, d_d, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(org, d_o, n * 16, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(dir, d_d, n * 16, cudaMemcpyDeviceToHost);
+    cudaFree(d_xy), cudaFree(d_u), cudaFree(d_o), cudaFree(d_d);
+    if (e != cudaSuccess) return set_err(AKB_CUDA_ERROR, "akb_generate_rays: %s", cudaGetErrorString(e));
+    return AKB_OK;
+}
+
+akb_status akb_film_to_srgb8(const float *rgbw, int32_t width, int32_t height, uint8_t *out_rgb8) {
+    akb_status st = check_ready("akb_film_to_srgb8");
+    if (st != AKB_OK) return st;
+    if (!rgbw || !out_rgb8 || width <= 0 || height <= 0) return set_err(AKB_INVALID_ARG, "akb_film_to_srgb8: bad argument");
+    const size_t n = (size_t)width * height;
+    float4 *d_in = nullptr;
+    uint8_t *d_out = nullptr;
+    cudaError_t e = cudaMalloc((void **)&d_in, n * 16);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&d_out, n * 3);
+    if (e == cudaSuccess) e = cudaMemcpy(d_in, rgbw, n * 16, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = launch_film_to_srgb8(d_in, n, d_out, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(out_rgb8, d_out, n * 3, cudaMemcpyDeviceToHost);
+    cudaFree(d_in), cudaFree(d_out);
+    if (e != cudaSuccess) return set_err(AKB_CUDA_ERROR, "akb_film_to_srgb8: %s", cudaGetErrorString(e));
+    return AKB_OK;
+}
+
+} // extern "C"

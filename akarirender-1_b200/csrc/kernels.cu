@@ -1,0 +1,470 @@
+// kernels.cu — hand-written sm_100a kernels of the Path hot path (no Triton/OptiX, no tensor cores: this is
+// latency/issue/L2-bound pointer-light traversal + shading, not a dense contraction).
+//
+// Wavefront organisation (replaces render_tile_wavefront, kernel/integrators/gpu/cuda/integrator.cpp:206-406, whose
+// 11 full-tile launches per bounce use state-predicated early-outs, no compaction and AoS managed memory):
+//   wf_init    : one slot per owned pixel; first camera ray of every pixel        ("Set Path State" + "Ray Generation")
+//   wf_trace   : ONE launch per bounce over the compacted extension-ray queue (closest hit, CWBVH traversal) AND the
+//                compacted shadow-ray queue of the previous bounce (any hit, adds the carried radiance to L);
+//                closest hits are binned by BSDF kind into material-keyed shading queues with warp-aggregated atomics
+//                ("Extension Ray" + "Shadow Ray" + "Hit Nothing")
+//   wf_shade   : ONE launch per bounce over the key-sorted shading queues (each key padded to a warp, so warps are
+//                material-homogeneous): BSDF build + sample, light select + sample, emits the next extension ray and
+//                the shadow ray; finished paths add to the film accumulator and regenerate the pixel's next sample
+//                in place ("Evaluate Material" x3 + "Splat" + "Ray Generation")
+//   wf_resolve : slot accumulators -> pixel-indexed film (Film::merge_tile)
+// All queue lengths live in HBM (Counters); kernels run a fixed persistent grid and read them, so a bounce costs two
+// launches and no host round trip.
+#include "kernels.cuh"
+
+#include <algorithm>
+
+namespace akb {
+namespace {
+
+constexpr int kBlock = 128;
+constexpr uint32_t kDeadRay = 0x80000000u; // queue-entry flag: path ends at the next shade step, nothing to trace
+
+__device__ __forceinline__ v3 xyz(const float4 &a) { return mk3(a.x, a.y, a.z); }
+__device__ __forceinline__ float4 mk4(v3 a, float w) { return make_float4(a.x, a.y, a.z, w); }
+__device__ __forceinline__ unsigned lanemask_lt() {
+    unsigned m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// Warp-aggregated queue append; must be reached by all 32 lanes. One atomic per warp.
+__device__ __forceinline__ void queue_push(bool pred, uint32_t value, uint32_t *queue, uint32_t *counter) {
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0) return;
+    const int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if ((int)(threadIdx.x & 31) == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (pred) queue[base + __popc(m & lanemask_lt())] = value;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void selftest_kernel(int *result, float a, float b, float c) {
+    // (1+2^-12)^2 = 1 + 2^-11 + 2^-24 rounds to 1 + 2^-11, so a*b + c == 0 unless the compiler fused it (2^-24).
+    float r = a * b + c;
+    *result = (r == 0.0f) ? 1 : 0;
+}
+
+template <bool ANY>
+__global__ void __launch_bounds__(kBlock)
+    trace_batch_kernel(SceneDev S, const float4 *__restrict__ org, const float4 *__restrict__ dir, size_t n,
+                       akb_hit *__restrict__ hits, int32_t *__restrict__ occ) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float4 o = __ldcs(org + i), d = __ldcs(dir + i);
+        RayHit h;
+        const bool r = traverse8<ANY>(S.nodes, S.tris, xyz(o), xyz(d), o.w, d.w, h);
+        if (ANY) {
+            __stcs(occ + i, r ? 1 : 0);
+        } else {
+            akb_hit out;
+            if (r) {
+                const float4 *sr = S.shading + 6 * (size_t)h.tri;
+                out.t = h.t, out.u = h.u, out.v = h.v;
+                out.geom_id = (int)__float_as_uint(__ldg(sr + 4).w);
+                out.prim_id = (int)__float_as_uint(__ldg(sr + 5).w);
+            } else {
+                out.t = INFINITY, out.u = 0.f, out.v = 0.f, out.prim_id = -1, out.geom_id = -1;
+            }
+            hits[i] = out;
+        }
+    }
+}
+
+__global__ void generate_rays_kernel(SceneDev S, const int32_t *xy, const float *u2, size_t n, float4 *org, float4 *dir) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    v3 o, d;
+    camera_generate_ray(S.cam, u2[2 * i], u2[2 * i + 1], xy[2 * i], xy[2 * i + 1], o, d);
+    org[i] = mk4(o, AKB_EPS); // Ray ctor defaults, common/math.h:192-194
+    dir[i] = mk4(d, INFINITY);
+}
+
+// Film::write_image post-process (core/film.h:97-113): radiance/weight; linear_to_srgb in fp32 (common/color.h:57-61);
+// DefaultImageWriter (core/image.cpp:48-53): clamp to [0,1], (int)round(x * 255.5) in double, clamp to [0,255].
+// powf is evaluated in double and rounded once, like glibc's.
+__global__ void film_to_srgb8_kernel(const float4 *rgbw, size_t n, uint8_t *out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 p = rgbw[i];
+    const float c[3] = {p.x, p.y, p.z};
+    for (int k = 0; k < 3; k++) {
+        float L = c[k];
+        if (p.w != 0) L = L / p.w;
+        float v = (L < 0.0031308f) ? (L * 12.92f) : (1.055f * (float)pow((double)L, (double)(1.0f / 2.4f)) - 0.055f);
+        v = min_std(max_std(v, 0.0f), 1.0f);
+        int q = (int)round((double)v * 255.5);
+        out[3 * i + k] = (uint8_t)(q < 0 ? 0 : (q > 255 ? 255 : q));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Megakernel mode (Path { megakernel: true }): one thread per pixel runs GenericPathTracer::run_megakernel for all its
+// samples, exactly the loop of cpu::PathTracer::render (kernel/integrators/cpu/integrator.cpp:121-135).
+template <int SAMP>
+__global__ void __launch_bounds__(kBlock) megakernel(SceneDev S, RenderConfig rc, float4 *__restrict__ film, Counters *ctr) {
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    int x = 0, y = 0;
+    const bool valid = slot < rc.map.n_slots() && slot_to_pixel(rc.map, slot, x, y);
+    unsigned long long n_closest = 0, n_shadow = 0, n_samples = 0;
+    if (valid) {
+        Rng<SAMP> rng;
+        rng.set_sample_index((uint64_t)(x + y * rc.map.width));
+        v3 sum = mk3(0, 0, 0);
+        float weight = 0;
+        for (int s = 0; s < rc.spp; s++) {
+            PathState<SAMP> ps;
+            ps.L = mk3(0, 0, 0), ps.beta = mk3(1, 1, 1), ps.depth = 0, ps.rng = rng;
+            float u1x, u1y, u2x, u2y;
+            ps.rng.next2d(u2x, u2y); // g++ evaluates generate_ray's arguments right to left: u2 first
+            ps.rng.next2d(u1x, u1y);
+            RaySeg ray;
+            camera_generate_ray(S.cam, u2x, u2y, x, y, ray.o, ray.d);
+            ray.tmin = AKB_EPS, ray.tmax = INFINITY;
+            for (;;) {
+                RayHit hit;
+                n_closest++;
+                if (!traverse8<false>(S.nodes, S.tris, ray.o, ray.d, ray.tmin, ray.tmax, hit)) break;
+                RaySeg next, sh;
+                v3 sc;
+                const int fl = path_vertex<SAMP>(S, ps, ray.d, hit.u, hit.v, hit.tri, rc.max_depth, rc.rr_start, next, sh, sc);
+                if (fl & VTX_SHADOW) {
+                    RayHit dummy;
+                    n_shadow++;
+                    if (!traverse8<true>(S.nodes, S.tris, sh.o, sh.d, sh.tmin, sh.tmax, dummy)) ps.L = add3(ps.L, sc);
+                }
+                if (!(fl & VTX_CONTINUE)) break;
+                ray = next;
+            }
+            rng = ps.rng;
+            weight += 1.0f;
+            sum = add3(sum, clamp_sample(ps.L, rc.ray_clamp));
+            n_samples++;
+        }
+        film[(size_t)y * rc.map.width + x] = mk4(sum, weight);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        n_closest += __shfl_down_sync(0xffffffffu, n_closest, o);
+        n_shadow += __shfl_down_sync(0xffffffffu, n_shadow, o);
+        n_samples += __shfl_down_sync(0xffffffffu, n_samples, o);
+    }
+    if ((threadIdx.x & 31) == 0 && n_samples) {
+        atomicAdd(&ctr->stat_closest, n_closest);
+        atomicAdd(&ctr->stat_shadow, n_shadow);
+        atomicAdd(&ctr->stat_samples, n_samples);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Wavefront kernels.
+
+// Starts sample `done` of the pixel owning `slot`: camera ray + fresh path state ("Ray Generation",
+// gpu/cuda/integrator.cpp:236-256; sampler draw order of kernel/pathtracer.h:61-64 under g++).
+template <int SAMP>
+__device__ __forceinline__ void start_sample(const SceneDev &S, const Workspace &ws, int slot, int x, int y, Rng<SAMP> rng,
+                                             int done) {
+    float u1x, u1y, u2x, u2y;
+    rng.next2d(u2x, u2y);
+    rng.next2d(u1x, u1y);
+    v3 o, d;
+    camera_generate_ray(S.cam, u2x, u2y, x, y, o, d);
+    ws.ray_o[slot] = mk4(o, AKB_EPS);
+    ws.ray_d[slot] = mk4(d, INFINITY);
+    ws.beta[slot] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
+    ws.L[slot] = make_float4(0.f, 0.f, 0.f, __int_as_float(done));
+    ws.rng[slot] = rng.s;
+}
+
+template <int SAMP> __global__ void __launch_bounds__(256) wf_init_kernel(SceneDev S, RenderConfig rc, Workspace ws) {
+    const int n = ws.n_slots;
+    const int n_pad = (n + 31) & ~31;
+    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_pad; slot += gridDim.x * blockDim.x) {
+        int x = 0, y = 0;
+        const bool valid = slot < n && slot_to_pixel(rc.map, slot, x, y) && rc.spp > 0;
+        if (slot < n) ws.acc[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid) {
+            Rng<SAMP> rng;
+            rng.set_sample_index((uint64_t)(x + y * rc.map.width));
+            start_sample<SAMP>(S, ws, slot, x, y, rng, 0);
+        }
+        queue_push(valid, (uint32_t)slot, ws.q_ext[0], &ws.ctr->n_ext[0]);
+    }
+}
+
+template <int SAMP>
+__global__ void __launch_bounds__(kBlock) wf_trace_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
+    Counters *ctr = ws.ctr;
+    const uint32_t n_ext = ctr->n_ext[b], n_sh = ctr->n_sh[b];
+    const uint32_t ext_pad = (n_ext + 31u) & ~31u;
+    const uint32_t total = ext_pad + ((n_sh + 31u) & ~31u);
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+    uint32_t n_traced = 0, n_skipped = 0;
+    for (uint32_t base = warp * 32u; base < total; base += n_warps * 32u) {
+        const uint32_t i = base + lane;
+        if (base < ext_pad) { // closest hit
+            const bool valid = i < n_ext;
+            int key = 0;
+            uint32_t slot = 0;
+            if (valid) {
+                const uint32_t e = ws.q_ext[b][i];
+                slot = e & ~kDeadRay;
+                float4 hrec = make_float4(0.f, 0.f, __int_as_float(-1), __int_as_float(-1));
+                if (e & kDeadRay) {
+                    n_skipped++;
+                } else {
+                    const float4 o = ws.ray_o[slot], d = ws.ray_d[slot];
+                    RayHit h;
+                    n_traced++;
+                    if (traverse8<false>(S.nodes, S.tris, xyz(o), xyz(d), o.w, d.w, h)) {
+                        hrec = make_float4(h.u, h.v, __int_as_float(h.tri), __int_as_float(h.mat));
+                        if (rc.sort_materials && h.mat >= 0) {
+                            // BSDF kind this vertex will evaluate: resolve Mix with the number the shade step will draw
+                            // (second LCG/PCG draw from the path's current state = x of the next next2d()).
+                            int m = h.mat;
+                            int type = S.mats[m].type;
+                            if (type == AKB_MAT_MIX) {
+                                Rng<SAMP> peek;
+                                peek.s = ws.rng[slot];
+                                float ux, uy, cp;
+                                peek.next2d(ux, uy);
+                                type = S.mats[select_material(S.mats, m, ux, cp)].type;
+                            }
+                            key = type == AKB_MAT_DIFFUSE ? 1 : (type == AKB_MAT_GLOSSY ? 2 : (type == AKB_MAT_DIELECTRIC ? 3 : 0));
+                        }
+                    }
+                }
+                ws.hit[slot] = hrec;
+            }
+            // bin by key: one atomic per (warp, key)
+            const unsigned grp = __match_any_sync(0xffffffffu, valid ? key : 0xFF);
+            if (valid) {
+                const int leader = __ffs(grp) - 1;
+                uint32_t qb = 0;
+                if ((int)lane == leader) qb = atomicAdd(&ctr->n_shade[b][key], (uint32_t)__popc(grp));
+                qb = __shfl_sync(grp, qb, leader);
+                ws.q_shade[b][key][qb + __popc(grp & lanemask_lt())] = slot;
+            }
+        } else { // shadow rays emitted by the previous shade step
+            const uint32_t j = i - ext_pad;
+            if (j < n_sh) {
+                const uint32_t slot = ws.q_sh[b][j];
+                const float4 o = ws.sh_o[slot], d = ws.sh_d[slot];
+                RayHit h;
+                n_traced++;
+                if (!traverse8<true>(S.nodes, S.tris, xyz(o), xyz(d), o.w, d.w, h)) {
+                    const float4 c = ws.sh_c[slot];
+                    float4 L = ws.L[slot];
+                    const v3 s = add3(xyz(L), xyz(c)); // L += color, kernel/pathtracer.h:156
+                    L.x = s.x, L.y = s.y, L.z = s.z;
+                    ws.L[slot] = L;
+                }
+            }
+        }
+    }
+    (void)n_traced;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        // queues the NEXT shade step fills must start empty; nobody else touches them during this launch
+        ctr->n_ext[b ^ 1] = 0;
+        ctr->n_sh[b ^ 1] = 0;
+        ctr->stat_closest += n_ext; // includes parked entries; stat_skipped counts those
+        ctr->stat_shadow += n_sh;
+    }
+    for (int o = 16; o > 0; o >>= 1) n_skipped += __shfl_down_sync(0xffffffffu, n_skipped, o);
+    if (lane == 0 && n_skipped) atomicAdd(&ctr->stat_skipped, (unsigned long long)n_skipped);
+}
+
+template <int SAMP>
+__global__ void __launch_bounds__(kBlock) wf_shade_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
+    Counters *ctr = ws.ctr;
+    uint32_t seg[kNumKeys + 1];
+    uint32_t cnt[kNumKeys];
+    seg[0] = 0;
+#pragma unroll
+    for (int k = 0; k < kNumKeys; k++) {
+        cnt[k] = ctr->n_shade[b][k];
+        seg[k + 1] = seg[k] + ((cnt[k] + 31u) & ~31u);
+    }
+    const uint32_t total = seg[kNumKeys];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+    uint32_t n_done = 0;
+    for (uint32_t base = warp * 32u; base < total; base += n_warps * 32u) {
+        int k = 0;
+#pragma unroll
+        for (int q = 1; q < kNumKeys; q++)
+            if (base >= seg[q]) k = q;
+        const uint32_t j = base - seg[k] + lane;
+        const bool valid = j < cnt[k];
+        bool push_ext = false, push_sh = false;
+        uint32_t ext_entry = 0, slot = 0;
+        if (valid) {
+            slot = ws.q_shade[b][k][j];
+            ext_entry = slot;
+            const float4 hrec = ws.hit[slot];
+            const int tri = __float_as_int(hrec.z);
+            PathState<SAMP> ps;
+            ps.rng.s = ws.rng[slot];
+            ps.L = mk3(0, 0, 0); // running L stays in HBM; path_vertex only ever adds emission, at depth 0
+            bool finished = true; // path ends at this vertex
+            if (tri >= 0) {
+                const float4 bd = ws.beta[slot];
+                const float4 rd = ws.ray_d[slot];
+                ps.beta = xyz(bd), ps.depth = __float_as_int(bd.w);
+                RaySeg next, sh;
+                v3 sc;
+                const int fl = path_vertex<SAMP>(S, ps, xyz(rd), hrec.x, hrec.y, tri, rc.max_depth, rc.rr_start, next, sh, sc);
+                bool cont = (fl & VTX_CONTINUE) != 0;
+                const bool shadow = (fl & VTX_SHADOW) != 0;
+                // A ray leaving a vertex at depth == max_depth can never contribute (kernel/pathtracer.h:102-112: no
+                // emission at depth > 0, no scattering at depth >= max_depth): it is not traced.
+                if (cont && ps.depth >= rc.max_depth && ps.depth > 0) cont = false;
+                if (shadow) {
+                    ws.sh_o[slot] = mk4(sh.o, sh.tmin);
+                    ws.sh_d[slot] = mk4(sh.d, sh.tmax);
+                    ws.sh_c[slot] = mk4(sc, 0.f);
+                    push_sh = true;
+                }
+                if (cont) {
+                    ws.ray_o[slot] = mk4(next.o, next.tmin);
+                    ws.ray_d[slot] = mk4(next.d, next.tmax);
+                    ws.beta[slot] = mk4(ps.beta, __int_as_float(ps.depth));
+                    ws.rng[slot] = ps.rng.s;
+                    push_ext = true, finished = false;
+                } else if (shadow) {
+                    // the film add must wait for this vertex's shadow ray: park the path for one step
+                    ws.rng[slot] = ps.rng.s;
+                    ext_entry = slot | kDeadRay;
+                    push_ext = true, finished = false;
+                }
+            }
+            if (finished) { // "Splat" + regenerate (gpu/cuda/integrator.cpp:385-401, core/film.h:66-70)
+                const float4 Lr = ws.L[slot];
+                const v3 L = add3(xyz(Lr), ps.L); // ps.L != 0 only for a camera-visible emitter, where Lr.xyz == 0
+                const int done = __float_as_int(Lr.w) + 1;
+                float4 a = ws.acc[slot];
+                const v3 s = add3(xyz(a), clamp_sample(L, rc.ray_clamp));
+                ws.acc[slot] = make_float4(s.x, s.y, s.z, a.w + 1.0f);
+                n_done++;
+                if (done < rc.spp) {
+                    int x, y;
+                    slot_to_pixel(rc.map, (int)slot, x, y);
+                    start_sample<SAMP>(S, ws, (int)slot, x, y, ps.rng, done);
+                    push_ext = true;
+                }
+            }
+        }
+        queue_push(push_ext, ext_entry, ws.q_ext[b ^ 1], &ctr->n_ext[b ^ 1]);
+        queue_push(push_sh, slot, ws.q_sh[b ^ 1], &ctr->n_sh[b ^ 1]);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < kNumKeys; k++) ctr->n_shade[b ^ 1][k] = 0;
+    }
+    for (int o = 16; o > 0; o >>= 1) n_done += __shfl_down_sync(0xffffffffu, n_done, o);
+    if (lane == 0 && n_done) atomicAdd(&ctr->stat_samples, (unsigned long long)n_done);
+}
+
+__global__ void wf_resolve_kernel(RenderConfig rc, Workspace ws, float4 *__restrict__ film) {
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    int x, y;
+    if (slot < ws.n_slots && slot_to_pixel(rc.map, slot, x, y)) film[(size_t)y * rc.map.width + x] = ws.acc[slot];
+}
+
+template <class K> int blocks_per_sm(K kernel, int block) {
+    int n = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, block, 0) != cudaSuccess || n < 1) n = 1;
+    return n;
+}
+
+} // namespace
+
+cudaError_t launch_selftest(int *d_result, cudaStream_t st) {
+    const float a = 1.0f + 1.0f / 4096.0f;
+    selftest_kernel<<<1, 1, 0, st>>>(d_result, a, a, -(1.0f + 1.0f / 2048.0f));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_trace_batch(const SceneDev &S, const float4 *org, const float4 *dir, size_t n, int any_hit,
+                               akb_hit *hits, int32_t *occ, int n_sms, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    static int occ_c = blocks_per_sm(trace_batch_kernel<false>, kBlock), occ_a = blocks_per_sm(trace_batch_kernel<true>, kBlock);
+    size_t want = (n + kBlock - 1) / kBlock;
+    int grid = (int)std::min<size_t>(want, (size_t)n_sms * (any_hit ? occ_a : occ_c));
+    if (any_hit)
+        trace_batch_kernel<true><<<grid, kBlock, 0, st>>>(S, org, dir, n, hits, occ);
+    else
+        trace_batch_kernel<false><<<grid, kBlock, 0, st>>>(S, org, dir, n, hits, occ);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_generate_rays(const SceneDev &S, const int32_t *xy, const float *u2, size_t n, float4 *org,
+                                 float4 *dir, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    generate_rays_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(S, xy, u2, n, org, dir);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_film_to_srgb8(const float4 *rgbw, size_t n, uint8_t *out, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    film_to_srgb8_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(rgbw, n, out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_megakernel(const SceneDev &S, const RenderConfig &rc, float4 *film, Counters *ctr, cudaStream_t st) {
+    const int n = rc.map.n_slots();
+    if (n == 0) return cudaSuccess;
+    const int grid = (n + kBlock - 1) / kBlock;
+    if (rc.sampler == AKB_SAMPLER_PCG)
+        megakernel<AKB_SAMPLER_PCG><<<grid, kBlock, 0, st>>>(S, rc, film, ctr);
+    else
+        megakernel<AKB_SAMPLER_LCG><<<grid, kBlock, 0, st>>>(S, rc, film, ctr);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wf_init(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int n_sms, cudaStream_t st) {
+    const int grid = std::max(1, std::min((ws.n_slots + 255) / 256, n_sms * 8));
+    if (rc.sampler == AKB_SAMPLER_PCG)
+        wf_init_kernel<AKB_SAMPLER_PCG><<<grid, 256, 0, st>>>(S, rc, ws);
+    else
+        wf_init_kernel<AKB_SAMPLER_LCG><<<grid, 256, 0, st>>>(S, rc, ws);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wf_trace(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int parity, int n_sms,
+                            cudaStream_t st) {
+    static int occ_l = blocks_per_sm(wf_trace_kernel<AKB_SAMPLER_LCG>, kBlock),
+               occ_p = blocks_per_sm(wf_trace_kernel<AKB_SAMPLER_PCG>, kBlock);
+    if (rc.sampler == AKB_SAMPLER_PCG)
+        wf_trace_kernel<AKB_SAMPLER_PCG><<<n_sms * occ_p, kBlock, 0, st>>>(S, rc, ws, parity);
+    else
+        wf_trace_kernel<AKB_SAMPLER_LCG><<<n_sms * occ_l, kBlock, 0, st>>>(S, rc, ws, parity);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wf_shade(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int parity, int n_sms,
+                            cudaStream_t st) {
+    static int occ_l = blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_LCG>, kBlock),
+               occ_p = blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_PCG>, kBlock);
+    if (rc.sampler == AKB_SAMPLER_PCG)
+        wf_shade_kernel<AKB_SAMPLER_PCG><<<n_sms * occ_p, kBlock, 0, st>>>(S, rc, ws, parity);
+    else
+        wf_shade_kernel<AKB_SAMPLER_LCG><<<n_sms * occ_l, kBlock, 0, st>>>(S, rc, ws, parity);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wf_resolve(const RenderConfig &rc, const Workspace &ws, float4 *film, cudaStream_t st) {
+    if (ws.n_slots == 0) return cudaSuccess;
+    wf_resolve_kernel<<<(ws.n_slots + 255) / 256, 256, 0, st>>>(rc, ws, film);
+    return cudaGetLastError();
+}
+
+} // namespace akb

@@ -1,0 +1,60 @@
+// kernels.cuh — launch interface of the sm_100a kernels (kernels.cu), used by the C ABI (api.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "scene_host.h"
+
+namespace akb {
+
+constexpr int kNumKeys = 4; // shading-queue keys: 0 terminate/other, 1 diffuse, 2 GGX, 3 dielectric
+
+// Device-resident counters of the wavefront (one struct in HBM). Index [2] = iteration parity.
+struct Counters {
+    uint32_t n_ext[2];             // extension-ray queue length
+    uint32_t n_sh[2];              // shadow-ray queue length
+    uint32_t n_shade[2][kNumKeys]; // material-keyed shading queues
+    uint32_t pad[4];
+    unsigned long long stat_closest, stat_shadow, stat_samples, stat_skipped;
+};
+
+// Path / ray state, vectorised SoA in HBM, indexed by slot (one slot per owned pixel; replaces the reference's
+// SOA<PathState>, RayQueue, ShadowRayQueue, MaterialQueue: kernel/integrators/gpu/workitem.h:27-107).
+struct Workspace {
+    int n_slots;
+    float4 *ray_o, *ray_d;      // extension ray: (o|tmin) (d|tmax)
+    float4 *hit;                // (u, v, tri id bits, material bits), tri < 0 = miss
+    float4 *beta;               // (beta | depth bits)
+    float4 *L;                  // (L | samples-done bits)
+    unsigned long long *rng;    // sampler state
+    float4 *sh_o, *sh_d, *sh_c; // shadow ray + the radiance it carries
+    float4 *acc;                // per-slot film accumulator (sum L | sum weight): Tile::add_sample
+    uint32_t *q_ext[2], *q_sh[2], *q_shade[2][kNumKeys];
+    Counters *ctr;
+};
+
+struct RenderConfig {
+    int spp, max_depth, rr_start, sampler, sort_materials;
+    float ray_clamp;
+    SlotMap map;
+};
+
+struct LaunchDims {
+    int n_sms, trace_blocks, shade_blocks;
+};
+
+cudaError_t launch_selftest(int *d_result, cudaStream_t st);
+cudaError_t launch_trace_batch(const SceneDev &S, const float4 *org, const float4 *dir, size_t n, int any_hit,
+                               akb_hit *hits, int32_t *occ, int n_sms, cudaStream_t st);
+cudaError_t launch_generate_rays(const SceneDev &S, const int32_t *xy, const float *u2, size_t n, float4 *org,
+                                 float4 *dir, cudaStream_t st);
+cudaError_t launch_film_to_srgb8(const float4 *rgbw, size_t n, uint8_t *out, cudaStream_t st);
+cudaError_t launch_megakernel(const SceneDev &S, const RenderConfig &rc, float4 *film, Counters *ctr, cudaStream_t st);
+
+cudaError_t launch_wf_init(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int n_sms, cudaStream_t st);
+cudaError_t launch_wf_trace(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int parity, int n_sms,
+                            cudaStream_t st);
+cudaError_t launch_wf_shade(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int parity, int n_sms,
+                            cudaStream_t st);
+cudaError_t launch_wf_resolve(const RenderConfig &rc, const Workspace &ws, float4 *film, cudaStream_t st);
+
+} // namespace akb

@@ -781,16 +781,18 @@ int akor_sampler_kat(int kind, uint64_t seed, int n, float *out, float *out_next
     return 0;
 }
 
-/* Film::write_image post-process (core/film.h:97-113, core/image.cpp:38-61, common/color.h:57-61):
- * radiance/weight -> sRGB OETF -> clamp(round(255.5 * x)) */
+/* Film::write_image post-process (core/film.h:97-113): radiance/weight; GammaCorrection -> linear_to_srgb in fp32
+ * (common/color.h:57-61: L*12.92 or 1.055*pow(L,1/2.4)-0.055, scalars converted to float by Array's operators);
+ * DefaultImageWriter (core/image.cpp:48-53): clamp to [0,1], (int)std::round(x * 255.5) in double, clamp to [0,255]. */
 void akor_film_to_srgb8(const float *rgbw, int w, int h, uint8_t *out) {
     for (size_t i = 0; i < (size_t)w * h; i++) {
         float wt = rgbw[4 * i + 3];
         for (int c = 0; c < 3; c++) {
             float L = rgbw[4 * i + c];
             if (wt != 0) L = L / wt;
-            float v = (L < (float)0.0031308) ? (float)(L * 12.92) : (float)(1.055 * (double)powf(L, 1.0f / 2.4f) - 0.055);
-            int q = (int)floorf(v * 255.5f);
+            float v = (L < 0.0031308f) ? (L * 12.92f) : (1.055f * powf(L, 1.0f / 2.4f) - 0.055f);
+            v = minf_(maxf_(v, 0.0f), 1.0f);
+            int q = (int)round((double)v * 255.5);
             out[3 * i + c] = (uint8_t)(q < 0 ? 0 : (q > 255 ? 255 : q));
         }
     }

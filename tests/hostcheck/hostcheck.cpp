@@ -161,3 +161,18 @@ int hc_render(void *hv, const akb_render_params *p, float *out, int threads) {
     return 0;
 }
 }
+
+// glibc sinf/cosf restatement (csrc/shade.h) against the host libm: returns the number of mismatches over n arguments
+extern "C" long hc_trig_mismatches(long n) {
+    long bad = 0;
+    unsigned s = 1;
+    for (long i = 0; i < n; i++) {
+        s = s * 1103515245u + 12345u;
+        float x = (float)s / 4294967296.0f * 8.0f - 1.0f;
+        if (i % 7 == 0) x *= 1e-3f;
+        if (i % 11 == 0) x *= 12.f;
+        if (sinf(x) != akb::sincosf_glibc(x, 0)) bad++;
+        if (cosf(x) != akb::sincosf_glibc(x, 1)) bad++;
+    }
+    return bad;
+}
