@@ -19,6 +19,7 @@ namespace {
 thread_local std::string g_err;
 int g_device = -1;
 int g_n_sms = 0;
+constexpr size_t kMaxBatch = (size_t)1 << 30;
 bool g_profile_stages = false;
 
 akb_status set_err(akb_status st, const char *fmt, ...) {
@@ -334,7 +335,11 @@ akb_status akb_trace_device(akb_scene *sc, const float *d_org, const float *d_di
         return set_err(AKB_INVALID_ARG, "akb_trace_device: null argument");
     cudaStream_t stream = (cudaStream_t)cuda_stream;
     if (ms_kernel) CU(cudaEventRecord(sc->ev0, stream));
-    CU(launch_trace_batch(sc->dev, (const float4 *)d_org, (const float4 *)d_dir, n, any_hit, d_hits, d_occ, g_n_sms, stream));
+    for (size_t off = 0; off < n; off += kMaxBatch) { // the kernel indexes rays with 32 bits
+        const size_t m = std::min(kMaxBatch, n - off);
+        CU(launch_trace_batch(sc->dev, (const float4 *)d_org + off, (const float4 *)d_dir + off, m, any_hit,
+                              d_hits ? d_hits + off : nullptr, d_occ ? d_occ + off : nullptr, &sc->d_ctr->fetch_trace, g_n_sms, stream));
+    }
     if (ms_kernel) CU(cudaEventRecord(sc->ev1, stream));
     CU(cudaStreamSynchronize(stream));
     if (ms_kernel) CU(cudaEventElapsedTime(ms_kernel, sc->ev0, sc->ev1));
@@ -359,7 +364,7 @@ akb_status akb_trace(akb_scene *sc, const float *org, const float *dir, size_t n
         const size_t m = std::min(chunk, n - off);
         e = cudaMemcpy(d_o, org + 4 * off, m * sizeof(float4), cudaMemcpyHostToDevice);
         if (e == cudaSuccess) e = cudaMemcpy(d_d, dir + 4 * off, m * sizeof(float4), cudaMemcpyHostToDevice);
-        if (e == cudaSuccess) e = launch_trace_batch(sc->dev, d_o, d_d, m, any_hit, (akb_hit *)d_out, (int32_t *)d_out, g_n_sms, 0);
+        if (e == cudaSuccess) e = launch_trace_batch(sc->dev, d_o, d_d, m, any_hit, (akb_hit *)d_out, (int32_t *)d_out, &sc->d_ctr->fetch_trace, g_n_sms, 0);
         if (e == cudaSuccess)
             e = cudaMemcpy(any_hit ? (void *)(out_occ + off) : (void *)(out_hits + off), d_out, m * out_elt, cudaMemcpyDeviceToHost);
     }

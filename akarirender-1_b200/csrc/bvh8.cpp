@@ -215,16 +215,24 @@ struct Collapser {
     Bvh8 &out;
     Collapser(const Builder &b_, Bvh8 &o) : b(b_), out(o) {}
 
+    // 8-bit quantisation of the child boxes on a per-node grid. The traversal evaluates plane distances as
+    // fma(32768 + q, 2^e/d, (p - o)/d - 32768 * 2^e/d) (traverse.h), whose constant term is rounded with an error of
+    // up to 2^-9 grid steps; every quantised plane therefore keeps a margin of 2^-8 steps beyond the (already padded)
+    // child box, and the grid itself starts 2^-7 extents below the node box so that the margin never hits the clamp.
     void quantise(Node8 &nd, const BNode &box, const int32_t *child, const int *slot_of, int k) {
-        double scale[3];
+        double scale[3], origin[3];
         for (int a = 0; a < 3; a++) {
-            nd.p[a] = box.lo[a];
             double ext = (double)box.hi[a] - (double)box.lo[a];
             if (!(ext > 0)) ext = 1e-30;
+            float pf = (float)((double)box.lo[a] - ext * (1.0 / 128.0));
+            if ((double)pf > (double)box.lo[a] - ext * (1.0 / 256.0)) pf = nextafterf(pf, -INFINITY);
+            nd.p[a] = pf;
+            origin[a] = (double)pf;
+            double span = ((double)box.hi[a] + ext * (1.0 / 128.0)) - origin[a];
             int ex;
-            double m = frexp(ext / 255.0, &ex); // ext/255 = m * 2^ex, m in [0.5,1)
+            double m = frexp(span / 255.0, &ex); // span/255 = m * 2^ex, m in [0.5,1)
             int e = (m == 0.5) ? ex - 1 : ex;
-            while (ldexp(255.0, e) < ext) e++;
+            while (ldexp(255.0, e) < span) e++;
             if (e < -126) e = -126;
             if (e > 127) e = 127;
             nd.e[a] = (uint8_t)(e + 127);
@@ -237,11 +245,11 @@ struct Collapser {
             const BNode &c = b.nodes[child[i]];
             int s = slot_of[i];
             for (int a = 0; a < 3; a++) {
-                double p = nd.p[a];
-                double q0 = floor(((double)c.lo[a] - p) / scale[a]);
-                double q1 = ceil(((double)c.hi[a] - p) / scale[a]);
-                while (q0 > 0 && p + q0 * scale[a] > (double)c.lo[a]) q0 -= 1;
-                while (q1 < 255 && p + q1 * scale[a] < (double)c.hi[a]) q1 += 1;
+                const double p = origin[a], margin = scale[a] * (1.0 / 256.0);
+                double q0 = floor(((double)c.lo[a] - p - margin) / scale[a]);
+                double q1 = ceil(((double)c.hi[a] - p + margin) / scale[a]);
+                while (q0 > 0 && p + q0 * scale[a] > (double)c.lo[a] - margin) q0 -= 1;
+                while (q1 < 255 && p + q1 * scale[a] < (double)c.hi[a] + margin) q1 += 1;
                 q0 = q0 < 0 ? 0 : (q0 > 255 ? 255 : q0);
                 q1 = q1 < 0 ? 0 : (q1 > 255 ? 255 : q1);
                 ql[a][s] = (uint8_t)q0;

@@ -51,22 +51,79 @@ __global__ void selftest_kernel(int *result, float a, float b, float c) {
     *result = (r == 0.0f) ? 1 : 0;
 }
 
-template <bool ANY>
-__global__ void __launch_bounds__(kBlock)
-    trace_batch_kernel(SceneDev S, const float4 *__restrict__ org, const float4 *__restrict__ dir, size_t n,
-                       akb_hit *__restrict__ hits, int32_t *__restrict__ occ) {
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+// ---------------------------------------------------------------------------------------------------------------------
+// Persistent traversal warps with ray replacement. Rays of one warp finish after very different numbers of node
+// visits (ncu on the first version: 7.9 of 32 lanes active per issued instruction), so a warp does not wait for its
+// slowest ray: whenever fewer than kRefillBelow lanes are still traversing, the finished lanes write their results
+// and fetch new rays from the queue (one atomic per refill), and the warp continues with all lanes busy.
+//   Src::load(i, T, tag)  -> true: T initialised for item i; false: the item needs no traversal (result ready)
+//   Src::complete(have, i, tag, T): called by all 32 lanes together; lanes with have == true consume their result
+constexpr int kRefillBelow = 20;
+
+template <class Src>
+__device__ __forceinline__ void persistent_trace(const float4 *__restrict__ nodes, const float4 *__restrict__ tris, Src &src,
+                                                 uint32_t total, uint32_t *cursor) {
+    const unsigned lane = threadIdx.x & 31;
+    uint2 stack[kStackSize];
+    Trav T;
+    T.hit.tri = -1, T.hit.mat = -1, T.hit.u = T.hit.v = 0.f, T.hit.t = INFINITY, T.any = false;
+    bool active = false, have = false, exhausted = false;
+    uint32_t item = 0, tag = 0;
+    for (;;) {
+        src.complete(have, item, tag, T);
+        have = false;
+        if (!exhausted) {
+            const unsigned idle = __ballot_sync(0xffffffffu, !active);
+            if (idle) {
+                const int leader = __ffs(idle) - 1;
+                uint32_t base = 0;
+                if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)__popc(idle));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (base + (uint32_t)__popc(idle) >= total) exhausted = true;
+                if (!active) {
+                    const uint32_t i = base + (uint32_t)__popc(idle & lanemask_lt());
+                    if (i < total) {
+                        item = i;
+                        if (src.load(i, T, tag))
+                            active = true;
+                        else
+                            have = true;
+                    }
+                }
+            }
+        }
+        unsigned act = __ballot_sync(0xffffffffu, active);
+        if (act == 0) {
+            if (__any_sync(0xffffffffu, have)) continue;
+            if (exhausted) break;
+            continue;
+        }
+        do {
+            if (active && trav_step(T, nodes, tris, stack)) active = false, have = true;
+            act = __ballot_sync(0xffffffffu, active);
+        } while (act != 0 && (exhausted || __popc(act) >= kRefillBelow));
+    }
+}
+
+struct BatchSrc {
+    const float4 *org, *dir, *shading;
+    akb_hit *hits;
+    int32_t *occ;
+    bool any;
+    __device__ __forceinline__ bool load(uint32_t i, Trav &T, uint32_t &) const {
         const float4 o = __ldcs(org + i), d = __ldcs(dir + i);
-        RayHit h;
-        const bool r = traverse8<ANY>(S.nodes, S.tris, xyz(o), xyz(d), o.w, d.w, h);
-        if (ANY) {
-            __stcs(occ + i, r ? 1 : 0);
+        trav_init(T, xyz(o), xyz(d), o.w, d.w, any);
+        return true;
+    }
+    __device__ __forceinline__ void complete(bool have, uint32_t i, uint32_t, const Trav &T) const {
+        if (!have) return;
+        if (any) {
+            __stcs(occ + i, T.hit.tri >= 0 ? 1 : 0);
         } else {
             akb_hit out;
-            if (r) {
-                const float4 *sr = S.shading + 6 * (size_t)h.tri;
-                out.t = h.t, out.u = h.u, out.v = h.v;
+            if (T.hit.tri >= 0) {
+                const float4 *sr = shading + 6 * (size_t)T.hit.tri;
+                out.t = T.hit.t, out.u = T.hit.u, out.v = T.hit.v;
                 out.geom_id = (int)__float_as_uint(__ldg(sr + 4).w);
                 out.prim_id = (int)__float_as_uint(__ldg(sr + 5).w);
             } else {
@@ -75,6 +132,13 @@ __global__ void __launch_bounds__(kBlock)
             hits[i] = out;
         }
     }
+};
+
+__global__ void __launch_bounds__(kBlock)
+    trace_batch_kernel(SceneDev S, const float4 *__restrict__ org, const float4 *__restrict__ dir, uint32_t n, int any_hit,
+                       akb_hit *__restrict__ hits, int32_t *__restrict__ occ, uint32_t *cursor) {
+    BatchSrc src{org, dir, S.shading, hits, occ, any_hit != 0};
+    persistent_trace(S.nodes, S.tris, src, n, cursor);
 }
 
 __global__ void generate_rays_kernel(SceneDev S, const int32_t *xy, const float *u2, size_t n, float4 *org, float4 *dir) {
@@ -197,106 +261,107 @@ template <int SAMP> __global__ void __launch_bounds__(256) wf_init_kernel(SceneD
     }
 }
 
+// One launch per bounce: items [0, n_ext) are extension rays (closest hit), [n_ext, n_ext + n_sh) the shadow rays the
+// previous shade step emitted (any hit; unoccluded ones add their carried radiance to the path's L).
+template <int SAMP> struct WfSrc {
+    const SceneDev &S;
+    const RenderConfig &rc;
+    const Workspace &ws;
+    int b;
+    uint32_t n_ext;
+    __device__ __forceinline__ bool load(uint32_t i, Trav &T, uint32_t &slot) const {
+        if (i < n_ext) {
+            const uint32_t e = ws.q_ext[b][i];
+            slot = e & ~kDeadRay;
+            if (e & kDeadRay) { // parked path: nothing to trace, the shade step just finishes it
+                T.hit.tri = -1, T.hit.mat = -1, T.any = false;
+                return false;
+            }
+            const float4 o = ws.ray_o[slot], d = ws.ray_d[slot];
+            trav_init(T, xyz(o), xyz(d), o.w, d.w, false);
+        } else {
+            slot = ws.q_sh[b][i - n_ext];
+            const float4 o = ws.sh_o[slot], d = ws.sh_d[slot];
+            trav_init(T, xyz(o), xyz(d), o.w, d.w, true);
+        }
+        return true;
+    }
+    __device__ __forceinline__ void complete(bool have, uint32_t, uint32_t slot, const Trav &T) const {
+        const unsigned lane = threadIdx.x & 31;
+        int key = 0xFF;
+        if (have) {
+            if (!T.any) {
+                ws.hit[slot] = make_float4(T.hit.u, T.hit.v, __int_as_float(T.hit.tri), __int_as_float(T.hit.mat));
+                if (rc.sort_materials) {
+                    key = 0;
+                    if (T.hit.tri >= 0 && T.hit.mat >= 0) {
+                        // BSDF kind this vertex will evaluate: resolve Mix with the number the shade step will draw
+                        // (second draw from the path's current sampler state = x of the next next2d()).
+                        int type = S.mats[T.hit.mat].type;
+                        if (type == AKB_MAT_MIX) {
+                            Rng<SAMP> peek;
+                            peek.s = ws.rng[slot];
+                            float ux, uy, cp;
+                            peek.next2d(ux, uy);
+                            type = S.mats[select_material(S.mats, T.hit.mat, ux, cp)].type;
+                        }
+                        key = type == AKB_MAT_DIFFUSE ? 1 : (type == AKB_MAT_GLOSSY ? 2 : (type == AKB_MAT_DIELECTRIC ? 3 : 0));
+                    }
+                }
+            } else if (T.hit.tri < 0) { // unoccluded: L += color, kernel/pathtracer.h:156
+                const float4 c = ws.sh_c[slot];
+                float4 L = ws.L[slot];
+                const v3 s = add3(xyz(L), xyz(c));
+                L.x = s.x, L.y = s.y, L.z = s.z;
+                ws.L[slot] = L;
+            }
+        }
+        if (rc.sort_materials) { // bin closest hits by BSDF kind: one atomic per (warp, key)
+            const unsigned grp = __match_any_sync(0xffffffffu, key);
+            if (key != 0xFF) {
+                const int leader = __ffs(grp) - 1;
+                uint32_t qb = 0;
+                if ((int)lane == leader) qb = atomicAdd(&ws.ctr->n_shade[b][key], (uint32_t)__popc(grp));
+                qb = __shfl_sync(grp, qb, leader);
+                ws.q_shade[b][key][qb + __popc(grp & lanemask_lt())] = slot;
+            }
+        }
+    }
+};
+
 template <int SAMP>
 __global__ void __launch_bounds__(kBlock) wf_trace_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
     Counters *ctr = ws.ctr;
     const uint32_t n_ext = ctr->n_ext[b], n_sh = ctr->n_sh[b];
-    const uint32_t ext_pad = (n_ext + 31u) & ~31u;
-    const uint32_t total = ext_pad + ((n_sh + 31u) & ~31u);
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
-    uint32_t n_traced = 0, n_skipped = 0;
-    for (uint32_t base = warp * 32u; base < total; base += n_warps * 32u) {
-        const uint32_t i = base + lane;
-        if (base < ext_pad) { // closest hit
-            const bool valid = i < n_ext;
-            int key = 0;
-            uint32_t slot = 0;
-            if (valid) {
-                const uint32_t e = ws.q_ext[b][i];
-                slot = e & ~kDeadRay;
-                float4 hrec = make_float4(0.f, 0.f, __int_as_float(-1), __int_as_float(-1));
-                if (e & kDeadRay) {
-                    n_skipped++;
-                } else {
-                    const float4 o = ws.ray_o[slot], d = ws.ray_d[slot];
-                    RayHit h;
-                    n_traced++;
-                    if (traverse8<false>(S.nodes, S.tris, xyz(o), xyz(d), o.w, d.w, h)) {
-                        hrec = make_float4(h.u, h.v, __int_as_float(h.tri), __int_as_float(h.mat));
-                        if (rc.sort_materials && h.mat >= 0) {
-                            // BSDF kind this vertex will evaluate: resolve Mix with the number the shade step will draw
-                            // (second LCG/PCG draw from the path's current state = x of the next next2d()).
-                            int m = h.mat;
-                            int type = S.mats[m].type;
-                            if (type == AKB_MAT_MIX) {
-                                Rng<SAMP> peek;
-                                peek.s = ws.rng[slot];
-                                float ux, uy, cp;
-                                peek.next2d(ux, uy);
-                                type = S.mats[select_material(S.mats, m, ux, cp)].type;
-                            }
-                            key = type == AKB_MAT_DIFFUSE ? 1 : (type == AKB_MAT_GLOSSY ? 2 : (type == AKB_MAT_DIELECTRIC ? 3 : 0));
-                        }
-                    }
-                }
-                ws.hit[slot] = hrec;
-            }
-            // bin by key: one atomic per (warp, key)
-            const unsigned grp = __match_any_sync(0xffffffffu, valid ? key : 0xFF);
-            if (valid) {
-                const int leader = __ffs(grp) - 1;
-                uint32_t qb = 0;
-                if ((int)lane == leader) qb = atomicAdd(&ctr->n_shade[b][key], (uint32_t)__popc(grp));
-                qb = __shfl_sync(grp, qb, leader);
-                ws.q_shade[b][key][qb + __popc(grp & lanemask_lt())] = slot;
-            }
-        } else { // shadow rays emitted by the previous shade step
-            const uint32_t j = i - ext_pad;
-            if (j < n_sh) {
-                const uint32_t slot = ws.q_sh[b][j];
-                const float4 o = ws.sh_o[slot], d = ws.sh_d[slot];
-                RayHit h;
-                n_traced++;
-                if (!traverse8<true>(S.nodes, S.tris, xyz(o), xyz(d), o.w, d.w, h)) {
-                    const float4 c = ws.sh_c[slot];
-                    float4 L = ws.L[slot];
-                    const v3 s = add3(xyz(L), xyz(c)); // L += color, kernel/pathtracer.h:156
-                    L.x = s.x, L.y = s.y, L.z = s.z;
-                    ws.L[slot] = L;
-                }
-            }
-        }
-    }
-    (void)n_traced;
+    WfSrc<SAMP> src{S, rc, ws, b, n_ext};
+    persistent_trace(S.nodes, S.tris, src, n_ext + n_sh, &ctr->fetch_trace);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         // queues the NEXT shade step fills must start empty; nobody else touches them during this launch
         ctr->n_ext[b ^ 1] = 0;
         ctr->n_sh[b ^ 1] = 0;
-        ctr->stat_closest += n_ext; // includes parked entries; stat_skipped counts those
+        ctr->stat_closest += n_ext; // includes parked entries; the shade step counts those in stat_skipped
         ctr->stat_shadow += n_sh;
     }
-    for (int o = 16; o > 0; o >>= 1) n_skipped += __shfl_down_sync(0xffffffffu, n_skipped, o);
-    if (lane == 0 && n_skipped) atomicAdd(&ctr->stat_skipped, (unsigned long long)n_skipped);
 }
 
 template <int SAMP>
 __global__ void __launch_bounds__(kBlock) wf_shade_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
     Counters *ctr = ws.ctr;
+    // Work list: with material sorting the kNumKeys keyed queues, each padded to a warp so that warps are
+    // material-homogeneous; without it the extension queue itself (every traced or parked path gets shaded).
     uint32_t seg[kNumKeys + 1];
     uint32_t cnt[kNumKeys];
     seg[0] = 0;
 #pragma unroll
     for (int k = 0; k < kNumKeys; k++) {
-        cnt[k] = ctr->n_shade[b][k];
+        cnt[k] = rc.sort_materials ? ctr->n_shade[b][k] : (k == 0 ? ctr->n_ext[b] : 0u);
         seg[k + 1] = seg[k] + ((cnt[k] + 31u) & ~31u);
     }
     const uint32_t total = seg[kNumKeys];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
-    uint32_t n_done = 0;
+    uint32_t n_done = 0, n_parked = 0;
     for (uint32_t base = warp * 32u; base < total; base += n_warps * 32u) {
         int k = 0;
 #pragma unroll
@@ -307,7 +372,7 @@ __global__ void __launch_bounds__(kBlock) wf_shade_kernel(SceneDev S, RenderConf
         bool push_ext = false, push_sh = false;
         uint32_t ext_entry = 0, slot = 0;
         if (valid) {
-            slot = ws.q_shade[b][k][j];
+            slot = (rc.sort_materials ? ws.q_shade[b][k][j] : ws.q_ext[b][j]) & ~kDeadRay;
             ext_entry = slot;
             const float4 hrec = ws.hit[slot];
             const int tri = __float_as_int(hrec.z);
@@ -326,7 +391,7 @@ __global__ void __launch_bounds__(kBlock) wf_shade_kernel(SceneDev S, RenderConf
                 const bool shadow = (fl & VTX_SHADOW) != 0;
                 // A ray leaving a vertex at depth == max_depth can never contribute (kernel/pathtracer.h:102-112: no
                 // emission at depth > 0, no scattering at depth >= max_depth): it is not traced.
-                if (cont && ps.depth >= rc.max_depth && ps.depth > 0) cont = false;
+                if (cont && ps.depth >= rc.max_depth && ps.depth > 0) cont = false, n_parked++;
                 if (shadow) {
                     ws.sh_o[slot] = mk4(sh.o, sh.tmin);
                     ws.sh_d[slot] = mk4(sh.d, sh.tmax);
@@ -368,9 +433,14 @@ __global__ void __launch_bounds__(kBlock) wf_shade_kernel(SceneDev S, RenderConf
     if (blockIdx.x == 0 && threadIdx.x == 0) {
 #pragma unroll
         for (int k = 0; k < kNumKeys; k++) ctr->n_shade[b ^ 1][k] = 0;
+        ctr->fetch_trace = 0; // the next traversal launch starts fetching at item 0
     }
-    for (int o = 16; o > 0; o >>= 1) n_done += __shfl_down_sync(0xffffffffu, n_done, o);
+    for (int o = 16; o > 0; o >>= 1) {
+        n_done += __shfl_down_sync(0xffffffffu, n_done, o);
+        n_parked += __shfl_down_sync(0xffffffffu, n_parked, o);
+    }
     if (lane == 0 && n_done) atomicAdd(&ctr->stat_samples, (unsigned long long)n_done);
+    if (lane == 0 && n_parked) atomicAdd(&ctr->stat_skipped, (unsigned long long)n_parked);
 }
 
 __global__ void wf_resolve_kernel(RenderConfig rc, Workspace ws, float4 *__restrict__ film) {
@@ -394,15 +464,15 @@ cudaError_t launch_selftest(int *d_result, cudaStream_t st) {
 }
 
 cudaError_t launch_trace_batch(const SceneDev &S, const float4 *org, const float4 *dir, size_t n, int any_hit,
-                               akb_hit *hits, int32_t *occ, int n_sms, cudaStream_t st) {
+                               akb_hit *hits, int32_t *occ, uint32_t *fetch_cursor, int n_sms, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
-    static int occ_c = blocks_per_sm(trace_batch_kernel<false>, kBlock), occ_a = blocks_per_sm(trace_batch_kernel<true>, kBlock);
+    if (n > 0x7fffffffu) return cudaErrorInvalidValue; // callers chunk
+    static int occ_b = blocks_per_sm(trace_batch_kernel, kBlock);
+    cudaError_t e = cudaMemsetAsync(fetch_cursor, 0, sizeof(uint32_t), st);
+    if (e != cudaSuccess) return e;
     size_t want = (n + kBlock - 1) / kBlock;
-    int grid = (int)std::min<size_t>(want, (size_t)n_sms * (any_hit ? occ_a : occ_c));
-    if (any_hit)
-        trace_batch_kernel<true><<<grid, kBlock, 0, st>>>(S, org, dir, n, hits, occ);
-    else
-        trace_batch_kernel<false><<<grid, kBlock, 0, st>>>(S, org, dir, n, hits, occ);
+    int grid = (int)std::min<size_t>(want, (size_t)n_sms * occ_b);
+    trace_batch_kernel<<<grid, kBlock, 0, st>>>(S, org, dir, (uint32_t)n, any_hit, hits, occ, fetch_cursor);
     return cudaGetLastError();
 }
 

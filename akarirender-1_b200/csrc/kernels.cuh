@@ -13,7 +13,8 @@ struct Counters {
     uint32_t n_ext[2];             // extension-ray queue length
     uint32_t n_sh[2];              // shadow-ray queue length
     uint32_t n_shade[2][kNumKeys]; // material-keyed shading queues
-    uint32_t pad[4];
+    uint32_t fetch_trace;          // work-fetch cursor of the persistent traversal warps (reset by the previous kernel)
+    uint32_t pad[3];
     unsigned long long stat_closest, stat_shadow, stat_samples, stat_skipped;
 };
 
@@ -44,7 +45,7 @@ struct LaunchDims {
 
 cudaError_t launch_selftest(int *d_result, cudaStream_t st);
 cudaError_t launch_trace_batch(const SceneDev &S, const float4 *org, const float4 *dir, size_t n, int any_hit,
-                               akb_hit *hits, int32_t *occ, int n_sms, cudaStream_t st);
+                               akb_hit *hits, int32_t *occ, uint32_t *fetch_cursor, int n_sms, cudaStream_t st);
 cudaError_t launch_generate_rays(const SceneDev &S, const int32_t *xy, const float *u2, size_t n, float4 *org,
                                  float4 *dir, cudaStream_t st);
 cudaError_t launch_film_to_srgb8(const float4 *rgbw, size_t n, uint8_t *out, cudaStream_t st);

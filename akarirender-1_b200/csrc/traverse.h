@@ -92,96 +92,132 @@ AKB_HD bool mt_test(v3 o, v3 d, float tmin, float tmax, const float4 &r0, const 
 
 constexpr int kStackSize = 32;
 
+// 32768 + byte j of w, built with one byte permute: the byte lands in mantissa bits 15..8 of 2^15 (0x47000000), so
+// no integer->float conversion (a quarter-rate XU instruction, 48 per node visit) is needed.
+#ifdef __CUDA_ARCH__
+#define AKB_Q2F(w, j) __uint_as_float(__byte_perm((w), 0x47000000u, 0x7404u | ((j) << 4)))
+#else
+#define AKB_Q2F(w, j) akb_u2f(0x47000000u | ((((w) >> (8 * (j))) & 0xFFu) << 8))
+#endif
+
+// Traversal state of one ray. `trav_step` performs one node visit (pop if needed, five 128-bit loads, eight
+// quantised slab tests, then the Moeller-Trumbore tests of the leaf triangles that were hit), so a kernel can
+// interleave fetching new rays for finished lanes (persistent warps with ray replacement).
+struct Trav {
+    v3 o, d;
+    float idx, idy, idz, tmin, tbest;
+    uint32_t oct_inv4;
+    uint2 ng;
+    int sp;
+    bool any;
+    RayHit hit;
+};
+
+AKB_HD void trav_init(Trav &T, v3 o, v3 d, float tmin, float tmax, bool any_hit) {
+    const float ooeps = 8.271806125530277e-25f; // 2^-80: keeps 1/d finite; far below any geometric scale
+    T.o = o, T.d = d;
+    T.idx = 1.0f / (fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+    T.idy = 1.0f / (fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+    T.idz = 1.0f / (fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+    T.oct_inv4 = (7u - ((T.idx < 0 ? 1u : 0u) | (T.idy < 0 ? 2u : 0u) | (T.idz < 0 ? 4u : 0u))) * 0x01010101u;
+    T.tmin = tmin, T.tbest = tmax;
+    T.ng.x = 0, T.ng.y = 0x80000000u;
+    T.sp = 0;
+    T.any = any_hit;
+    T.hit.tri = -1, T.hit.t = INFINITY, T.hit.u = 0.f, T.hit.v = 0.f, T.hit.mat = -1;
+}
+
+// Returns true when the ray is finished (closest: tree exhausted; any-hit: first accepted triangle, hit.tri = 0).
+AKB_HD bool trav_step(Trav &T, const float4 *__restrict__ nodes, const float4 *__restrict__ tris, uint2 *stack) {
+    uint2 ng = T.ng;
+    if (ng.y <= 0x00FFFFFFu) {
+        if (T.sp == 0) return true;
+        ng = stack[--T.sp];
+    }
+    const uint32_t oct_inv = T.oct_inv4 & 7u;
+    const uint32_t imask = ng.y & 0xFFu;
+    const int bit = akb_bfind(ng.y);
+    ng.y &= ~(1u << bit);
+    if (ng.y > 0x00FFFFFFu && T.sp < kStackSize) stack[T.sp++] = ng;
+    const uint32_t slot = (uint32_t)(bit - 24) ^ oct_inv;
+    const uint32_t rel = (uint32_t)akb_popc(imask & ~(0xFFFFFFFFu << slot));
+    const float4 *np = nodes + 5 * (size_t)(ng.x + rel);
+    const float4 n0 = AKB_LD4(np), n1 = AKB_LD4(np + 1), n2 = AKB_LD4(np + 2), n3 = AKB_LD4(np + 3), n4 = AKB_LD4(np + 4);
+    const uint32_t ew = akb_f2u(n0.w);
+    const float idx = T.idx, idy = T.idy, idz = T.idz;
+    const float adjx = akb_u2f((ew & 0xFFu) << 23) * idx;
+    const float adjy = akb_u2f(((ew >> 8) & 0xFFu) << 23) * idy;
+    const float adjz = akb_u2f(((ew >> 16) & 0xFFu) << 23) * idz;
+    // plane distance = q*adj + (p - o)*idir with q carried as 32768 + q: fold the offset into the constant term
+    // (its rounding error, <= 2^-9 of a grid step, is covered by the builder's quantisation margin)
+    const float orgx = fmaf(-32768.0f, adjx, (n0.x - T.o.x) * idx);
+    const float orgy = fmaf(-32768.0f, adjy, (n0.y - T.o.y) * idy);
+    const float orgz = fmaf(-32768.0f, adjz, (n0.z - T.o.z) * idz);
+    ng.x = akb_f2u(n1.x);
+    const uint32_t tri_base = akb_f2u(n1.y);
+    const float tmin = T.tmin, tbest = T.tbest;
+    uint32_t hitmask = 0;
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        const uint32_t meta4 = akb_f2u(half ? n1.w : n1.z);
+        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t inner_mask4 = akb_sext_s8x4(is_inner4 << 3);
+        const uint32_t bit_index4 = (meta4 ^ (T.oct_inv4 & inner_mask4)) & 0x1F1F1F1Fu;
+        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+        const uint32_t qlox = akb_f2u(half ? n2.y : n2.x), qloy = akb_f2u(half ? n2.w : n2.z);
+        const uint32_t qloz = akb_f2u(half ? n3.y : n3.x), qhix = akb_f2u(half ? n3.w : n3.z);
+        const uint32_t qhiy = akb_f2u(half ? n4.y : n4.x), qhiz = akb_f2u(half ? n4.w : n4.z);
+        const uint32_t nx = idx < 0 ? qhix : qlox, fx = idx < 0 ? qlox : qhix;
+        const uint32_t ny = idy < 0 ? qhiy : qloy, fy = idy < 0 ? qloy : qhiy;
+        const uint32_t nz = idz < 0 ? qhiz : qloz, fz = idz < 0 ? qloz : qhiz;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const float tlx = fmaf(AKB_Q2F(nx, j), adjx, orgx);
+            const float tly = fmaf(AKB_Q2F(ny, j), adjy, orgy);
+            const float tlz = fmaf(AKB_Q2F(nz, j), adjz, orgz);
+            const float thx = fmaf(AKB_Q2F(fx, j), adjx, orgx);
+            const float thy = fmaf(AKB_Q2F(fy, j), adjy, orgy);
+            const float thz = fmaf(AKB_Q2F(fz, j), adjz, orgz);
+            const float cmin = fmaxf(fmaxf(tlx, tly), fmaxf(tlz, tmin));
+            const float cmax = fminf(fminf(thx, thy), fminf(thz, tbest));
+            if (cmin <= cmax) hitmask |= ((child_bits4 >> (8 * j)) & 0xFFu) << ((bit_index4 >> (8 * j)) & 0xFFu);
+        }
+    }
+    ng.y = (hitmask & 0xFF000000u) | (ew >> 24);
+    uint32_t tmask = hitmask & 0x00FFFFFFu;
+    while (tmask) {
+        const int j = akb_bfind(tmask);
+        tmask &= ~(1u << j);
+        const float4 *tp = tris + 3 * (size_t)(tri_base + (uint32_t)j);
+        const float4 r0 = AKB_LD4(tp), r1 = AKB_LD4(tp + 1), r2 = AKB_LD4(tp + 2);
+        float t, u, v;
+        if (mt_test(T.o, T.d, T.tmin, T.any ? T.tbest : INFINITY, r0, r1, r2, t, u, v)) {
+            if (T.any) {
+                T.hit.tri = 0;
+                return true;
+            }
+            const int id = (int)akb_f2u(r0.w);
+            if (t < T.tbest || (t == T.tbest && T.hit.tri >= 0 && id < T.hit.tri)) {
+                T.tbest = t;
+                T.hit.t = t, T.hit.u = u, T.hit.v = v, T.hit.tri = id, T.hit.mat = (int)akb_f2u(r1.w);
+            }
+        }
+    }
+    T.ng = ng;
+    return ng.y <= 0x00FFFFFFu && T.sp == 0;
+}
+
+// Run one ray to completion (megakernel, tests/hostcheck).
 template <bool ANY>
 AKB_HD bool traverse8(const float4 *__restrict__ nodes, const float4 *__restrict__ tris, v3 o, v3 d, float tmin,
                       float tmax, RayHit &hit) {
-    const float ooeps = 8.271806125530277e-25f; // 2^-80: keeps 1/d finite; far below any geometric scale
-    const float idx = 1.0f / (fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
-    const float idy = 1.0f / (fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
-    const float idz = 1.0f / (fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
-    const uint32_t oct_inv = 7u - ((idx < 0 ? 1u : 0u) | (idy < 0 ? 2u : 0u) | (idz < 0 ? 4u : 0u));
-    const uint32_t oct_inv4 = oct_inv * 0x01010101u;
-
+    Trav T;
     uint2 stack[kStackSize];
-    int sp = 0;
-    uint2 ng;
-    ng.x = 0, ng.y = 0x80000000u;
-    float tbest = tmax;
-    hit.tri = -1, hit.t = INFINITY, hit.u = 0.f, hit.v = 0.f, hit.mat = -1;
-
-    for (;;) {
-        if (ng.y > 0x00FFFFFFu) {
-            const uint32_t imask = ng.y & 0xFFu;
-            const int bit = akb_bfind(ng.y);
-            ng.y &= ~(1u << bit);
-            if (ng.y > 0x00FFFFFFu && sp < kStackSize) stack[sp++] = ng;
-            const uint32_t slot = (uint32_t)(bit - 24) ^ oct_inv;
-            const uint32_t rel = (uint32_t)akb_popc(imask & ~(0xFFFFFFFFu << slot));
-            const float4 *np = nodes + 5 * (size_t)(ng.x + rel);
-            const float4 n0 = AKB_LD4(np), n1 = AKB_LD4(np + 1), n2 = AKB_LD4(np + 2), n3 = AKB_LD4(np + 3),
-                         n4 = AKB_LD4(np + 4);
-            const uint32_t ew = akb_f2u(n0.w);
-            const float adjx = akb_u2f((ew & 0xFFu) << 23) * idx;
-            const float adjy = akb_u2f(((ew >> 8) & 0xFFu) << 23) * idy;
-            const float adjz = akb_u2f(((ew >> 16) & 0xFFu) << 23) * idz;
-            const float orgx = (n0.x - o.x) * idx, orgy = (n0.y - o.y) * idy, orgz = (n0.z - o.z) * idz;
-            ng.x = akb_f2u(n1.x);
-            const uint32_t tri_base = akb_f2u(n1.y);
-            uint32_t hitmask = 0;
-#pragma unroll
-            for (int half = 0; half < 2; half++) {
-                const uint32_t meta4 = akb_f2u(half ? n1.w : n1.z);
-                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                const uint32_t inner_mask4 = akb_sext_s8x4(is_inner4 << 3);
-                const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1F1F1F1Fu;
-                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-                const uint32_t qlox = akb_f2u(half ? n2.y : n2.x), qloy = akb_f2u(half ? n2.w : n2.z);
-                const uint32_t qloz = akb_f2u(half ? n3.y : n3.x), qhix = akb_f2u(half ? n3.w : n3.z);
-                const uint32_t qhiy = akb_f2u(half ? n4.y : n4.x), qhiz = akb_f2u(half ? n4.w : n4.z);
-                const uint32_t nx = idx < 0 ? qhix : qlox, fx = idx < 0 ? qlox : qhix;
-                const uint32_t ny = idy < 0 ? qhiy : qloy, fy = idy < 0 ? qloy : qhiy;
-                const uint32_t nz = idz < 0 ? qhiz : qloz, fz = idz < 0 ? qloz : qhiz;
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const int sh = 8 * j;
-                    const float tlx = fmaf((float)((nx >> sh) & 0xFFu), adjx, orgx);
-                    const float tly = fmaf((float)((ny >> sh) & 0xFFu), adjy, orgy);
-                    const float tlz = fmaf((float)((nz >> sh) & 0xFFu), adjz, orgz);
-                    const float thx = fmaf((float)((fx >> sh) & 0xFFu), adjx, orgx);
-                    const float thy = fmaf((float)((fy >> sh) & 0xFFu), adjy, orgy);
-                    const float thz = fmaf((float)((fz >> sh) & 0xFFu), adjz, orgz);
-                    const float cmin = fmaxf(fmaxf(tlx, tly), fmaxf(tlz, tmin));
-                    const float cmax = fminf(fminf(thx, thy), fminf(thz, tbest));
-                    if (cmin <= cmax) hitmask |= ((child_bits4 >> sh) & 0xFFu) << ((bit_index4 >> sh) & 0xFFu);
-                }
-            }
-            ng.y = (hitmask & 0xFF000000u) | (ew >> 24);
-            uint32_t tmask = hitmask & 0x00FFFFFFu;
-            while (tmask) {
-                const int j = akb_bfind(tmask);
-                tmask &= ~(1u << j);
-                const float4 *tp = tris + 3 * (size_t)(tri_base + (uint32_t)j);
-                const float4 r0 = AKB_LD4(tp), r1 = AKB_LD4(tp + 1), r2 = AKB_LD4(tp + 2);
-                float t, u, v;
-                if (ANY) {
-                    if (mt_test(o, d, tmin, tmax, r0, r1, r2, t, u, v)) return true;
-                } else {
-                    // bound = +inf so that an exact tie with the current best still reaches the id comparison
-                    if (mt_test(o, d, tmin, tmax, r0, r1, r2, t, u, v)) {
-                        const int id = (int)akb_f2u(r0.w);
-                        if (t < tbest || (t == tbest && hit.tri >= 0 && id < hit.tri)) {
-                            tbest = t;
-                            hit.t = t, hit.u = u, hit.v = v, hit.tri = id, hit.mat = (int)akb_f2u(r1.w);
-                        }
-                    }
-                }
-            }
-        } else {
-            if (sp == 0) break;
-            ng = stack[--sp];
-        }
+    trav_init(T, o, d, tmin, tmax, ANY);
+    while (!trav_step(T, nodes, tris, stack)) {
     }
-    return hit.tri >= 0;
+    hit = T.hit;
+    return T.hit.tri >= 0;
 }
 
 } // namespace akb
