@@ -156,6 +156,14 @@ akb_status akb_init(int device_index) {
     if (h_res != 1) return set_err(AKB_CUDA_ERROR, "akb_init: kernels were built with FMA contraction; rebuild with -fmad=false");
     const char *pf = getenv("AKB_PROFILE_STAGES");
     g_profile_stages = pf && pf[0] == '1';
+    if (const char *rb = getenv("AKB_REFILL_BELOW")) {
+        int v = atoi(rb);
+        if (v >= 1 && v <= 32) CU(set_refill_below(v));
+    }
+    if (const char *fc = getenv("AKB_FETCH_CHUNK")) {
+        int v = atoi(fc);
+        if (v >= 0 && v <= 4096) CU(set_fetch_chunk(v));
+    }
     g_device = device_index;
     return AKB_OK;
 }

@@ -18,7 +18,8 @@ namespace {
 struct BNode {
     float lo[3], hi[3];
     int32_t left, right; // -1 for leaves
-    int32_t first, count;
+    int32_t first, count; // count > 0 only for binary leaves
+    int32_t n_prims;      // triangles below this node: idx[first .. first + n_prims)
 };
 
 inline float half_area(const float *lo, const float *hi) {
@@ -133,7 +134,7 @@ struct Builder {
         BNode &nd = nodes[id];
         bounds(first, count, nd.lo, nd.hi, clo, chi);
         nd.left = nd.right = -1;
-        nd.first = first, nd.count = count;
+        nd.first = first, nd.count = count, nd.n_prims = count;
     }
 
     void build_subtree(int32_t id) { // node `id` initialised as a leaf over [first, first+count)
@@ -258,7 +259,73 @@ struct Collapser {
         }
     }
 
+    // Optimal collapse of the binary tree into 8-wide nodes (dynamic programme of Ylitie et al. 2017, §3.1):
+    //   C(n,1) = min(C_leaf(n), C_internal(n));  C(n,i) = min(C_distribute(n,i), C(n,i-1))
+    //   C_leaf(n) = A_n * P_n * c_prim (P_n <= 3);  C_internal(n) = C_distribute(n,8) + A_n * c_node
+    //   C_distribute(n,j) = min_{0<k<j} C(left,k) + C(right,j-k)
+    // cost[n][i-1] = C(n,i); split[n][i-1] = k of the best distribution for i roots (0: use C(n,i-1));
+    // kind[n]: the single-root choice (leaf or wide node); split8[n]: k of C_distribute(n,8).
+    static constexpr float kNodeCost = 1.0f, kPrimCost = 0.3f;
+    std::vector<float> cost;
+    std::vector<uint8_t> split, split8, kind;
+
+    void solve() {
+        const int32_t nn = b.n_nodes.load();
+        cost.assign((size_t)nn * 7, INFINITY);
+        split.assign((size_t)nn * 7, 0);
+        split8.assign(nn, 0);
+        kind.assign(nn, 0);
+        for (int32_t n = nn - 1; n >= 0; n--) { // children always have larger indices than their parent
+            const BNode &nd = b.nodes[n];
+            const float area = half_area(nd.lo, nd.hi);
+            float *c = &cost[(size_t)n * 7];
+            const float c_leaf = nd.n_prims <= kMaxLeaf ? area * (float)nd.n_prims * kPrimCost : INFINITY;
+            if (nd.left < 0) {
+                for (int i = 0; i < 7; i++) c[i] = c_leaf;
+                kind[n] = 0;
+                continue;
+            }
+            const float *cl = &cost[(size_t)nd.left * 7], *cr = &cost[(size_t)nd.right * 7];
+            auto distribute = [&](int j, uint8_t &best_k) { // j roots in total, 1..j-1 on the left (capped at 7 each)
+                float best = INFINITY;
+                for (int k = 1; k < j; k++) {
+                    if (k > 7 || j - k > 7) continue;
+                    float v = cl[k - 1] + cr[j - k - 1];
+                    if (v < best) best = v, best_k = (uint8_t)k;
+                }
+                return best;
+            };
+            uint8_t k8 = 1;
+            const float c_internal = distribute(8, k8) + area * kNodeCost;
+            split8[n] = k8;
+            if (c_leaf <= c_internal)
+                c[0] = c_leaf, kind[n] = 0;
+            else
+                c[0] = c_internal, kind[n] = 1;
+            for (int i = 2; i <= 7; i++) {
+                uint8_t k = 1;
+                float d = distribute(i, k);
+                if (d < c[i - 2])
+                    c[i - 1] = d, split[(size_t)n * 7 + i - 1] = k;
+                else
+                    c[i - 1] = c[i - 2], split[(size_t)n * 7 + i - 1] = 0;
+            }
+        }
+    }
+    void gather(int32_t n, int i, int32_t *child, int &k) const {
+        while (i > 1 && split[(size_t)n * 7 + i - 1] == 0) i--;
+        if (i == 1) {
+            child[k++] = n;
+            return;
+        }
+        const int kl = split[(size_t)n * 7 + i - 1];
+        gather(b.nodes[n].left, kl, child, k);
+        gather(b.nodes[n].right, i - kl, child, k);
+    }
+    bool is_leaf_child(int32_t n) const { return kind[n] == 0; }
+
     void run() {
+        solve();
         out.nodes.clear();
         out.tri_order.clear();
         out.tri_order.reserve(b.n);
@@ -279,28 +346,16 @@ struct Collapser {
             const BNode &bn = b.nodes[it.bnode];
             int32_t child[8];
             int k = 0;
-            if (bn.left < 0) {
-                child[k++] = it.bnode; // root that is itself a leaf
+            if (bn.left < 0 || (it.bnode == 0 && kind[0] == 0)) {
+                child[k++] = it.bnode; // the whole scene fits one leaf
             } else {
-                child[k++] = bn.left, child[k++] = bn.right;
-                while (k < 8) { // open the internal child with the largest surface area
-                    int best = -1;
-                    float best_a = -1;
-                    for (int i = 0; i < k; i++) {
-                        const BNode &c = b.nodes[child[i]];
-                        if (c.left < 0) continue;
-                        float a = half_area(c.lo, c.hi);
-                        if (a > best_a) best_a = a, best = i;
-                    }
-                    if (best < 0) break;
-                    int32_t o = child[best];
-                    child[best] = b.nodes[o].left;
-                    child[k++] = b.nodes[o].right;
-                }
+                const int kl = split8[it.bnode];
+                gather(bn.left, kl, child, k);
+                gather(bn.right, 8 - kl, child, k);
             }
             // slot assignment: slot s (bit0=x, bit1=y, bit2=z) should hold the child lying furthest towards
             // the (+/-,+/-,+/-) corner s, so that `slot ^ ray_octant` enumerates children front to back.
-            float cost[8][8];
+            float cst[8][8];
             float nc[3];
             for (int a = 0; a < 3; a++) nc[a] = 0.5f * (bn.lo[a] + bn.hi[a]);
             for (int i = 0; i < k; i++) {
@@ -308,7 +363,7 @@ struct Collapser {
                 float d[3];
                 for (int a = 0; a < 3; a++) d[a] = 0.5f * (c.lo[a] + c.hi[a]) - nc[a];
                 for (int s = 0; s < 8; s++)
-                    cost[i][s] = ((s & 1) ? d[0] : -d[0]) + ((s & 2) ? d[1] : -d[1]) + ((s & 4) ? d[2] : -d[2]);
+                    cst[i][s] = ((s & 1) ? d[0] : -d[0]) + ((s & 2) ? d[1] : -d[1]) + ((s & 4) ? d[2] : -d[2]);
             }
             int slot_of[8];
             bool cdone[8] = {false}, sdone[8] = {false};
@@ -318,7 +373,7 @@ struct Collapser {
                 for (int i = 0; i < k; i++) {
                     if (cdone[i]) continue;
                     for (int s = 0; s < 8; s++)
-                        if (!sdone[s] && cost[i][s] > bc) bc = cost[i][s], bi = i, bs = s;
+                        if (!sdone[s] && cst[i][s] > bc) bc = cst[i][s], bi = i, bs = s;
                 }
                 cdone[bi] = sdone[bs] = true;
                 slot_of[bi] = bs;
@@ -337,23 +392,25 @@ struct Collapser {
                 int i = child_in_slot[s];
                 if (i < 0) continue;
                 const BNode &c = b.nodes[child[i]];
-                if (c.left >= 0) {
+                const bool leaf = is_leaf_child(child[i]) || (it.bnode == child[i]);
+                if (!leaf) {
                     nd.imask |= (uint8_t)(1u << s);
                     nd.meta[s] = (uint8_t)((1u << 5) | (24u + (unsigned)s));
                     n_internal++;
                 } else {
-                    nd.meta[s] = (uint8_t)((unary(c.count) << 5) | (unsigned)tri_off);
-                    for (int32_t t = c.first; t < c.first + c.count; t++) out.tri_order.push_back(b.idx[t]);
-                    tri_off += c.count;
-                    out.sah_cost += (double)c.count * half_area(c.lo, c.hi) / root_area;
+                    nd.meta[s] = (uint8_t)((unary(c.n_prims) << 5) | (unsigned)tri_off);
+                    for (int32_t t = c.first; t < c.first + c.n_prims; t++) out.tri_order.push_back(b.idx[t]);
+                    tri_off += c.n_prims;
+                    out.sah_cost += (double)c.n_prims * kPrimCost * half_area(c.lo, c.hi) / root_area;
                 }
             }
-            out.sah_cost += (double)kTraversalCost * half_area(bn.lo, bn.hi) / root_area;
+            out.sah_cost += (double)kNodeCost * half_area(bn.lo, bn.hi) / root_area;
             out.nodes.resize(out.nodes.size() + (size_t)n_internal);
             uint32_t ci = nd.child_base;
             for (int s = 0; s < 8; s++) {
                 int i = child_in_slot[s];
-                if (i < 0 || b.nodes[child[i]].left < 0) continue;
+                if (i < 0) continue;
+                if (is_leaf_child(child[i]) || it.bnode == child[i]) continue;
                 queue.push_back({child[i], ci++, it.depth + 1});
             }
             out.nodes[it.wnode] = nd;

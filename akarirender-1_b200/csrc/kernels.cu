@@ -58,7 +58,8 @@ __global__ void selftest_kernel(int *result, float a, float b, float c) {
 // and fetch new rays from the queue (one atomic per refill), and the warp continues with all lanes busy.
 //   Src::load(i, T, tag)  -> true: T initialised for item i; false: the item needs no traversal (result ready)
 //   Src::complete(have, i, tag, T): called by all 32 lanes together; lanes with have == true consume their result
-constexpr int kRefillBelow = 20;
+__constant__ int c_fetch_chunk = 0; // 0: reserve exactly the idle-lane count per refill; >0: warp-private chunks (AKB_FETCH_CHUNK)
+__constant__ int c_refill_below = 20; // tunable at init (AKB_REFILL_BELOW); 20 measured best on B200
 
 template <class Src>
 __device__ __forceinline__ void persistent_trace(const float4 *__restrict__ nodes, const float4 *__restrict__ tris, Src &src,
@@ -67,41 +68,50 @@ __device__ __forceinline__ void persistent_trace(const float4 *__restrict__ node
     uint2 stack[kStackSize];
     Trav T;
     T.hit.tri = -1, T.hit.mat = -1, T.hit.u = T.hit.v = 0.f, T.hit.t = INFINITY, T.any = false;
-    bool active = false, have = false, exhausted = false;
+    bool active = false, have = false;
     uint32_t item = 0, tag = 0;
+    uint32_t w_next = 0, w_end = 0; // warp-private reserved range of the queue (one atomic per kFetchChunk items)
+    bool drained = false;           // the global cursor has passed the end
+    const int refill_below = c_refill_below;
+    const uint32_t fetch_chunk = (uint32_t)c_fetch_chunk;
     for (;;) {
         src.complete(have, item, tag, T);
         have = false;
-        if (!exhausted) {
-            const unsigned idle = __ballot_sync(0xffffffffu, !active);
-            if (idle) {
-                const int leader = __ffs(idle) - 1;
+        const unsigned idle = __ballot_sync(0xffffffffu, !active);
+        if (idle && !(drained && w_next == w_end)) {
+            if (w_next == w_end) {
                 uint32_t base = 0;
-                if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)__popc(idle));
-                base = __shfl_sync(0xffffffffu, base, leader);
-                if (base + (uint32_t)__popc(idle) >= total) exhausted = true;
-                if (!active) {
-                    const uint32_t i = base + (uint32_t)__popc(idle & lanemask_lt());
-                    if (i < total) {
-                        item = i;
-                        if (src.load(i, T, tag))
-                            active = true;
-                        else
-                            have = true;
-                    }
-                }
+                const uint32_t want = fetch_chunk ? fetch_chunk : (uint32_t)__popc(idle);
+                if (lane == 0) base = atomicAdd(cursor, want);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                w_next = min(base, total), w_end = min(base + want, total);
+                if (w_end == total) drained = true;
             }
+            const uint32_t avail = w_end - w_next;
+            const uint32_t rank = (uint32_t)__popc(idle & lanemask_lt());
+            if (!active && rank < avail) {
+                item = w_next + rank;
+                if (src.load(item, T, tag))
+                    active = true;
+                else
+                    have = true;
+            }
+            w_next += min((uint32_t)__popc(idle), avail);
         }
+        const bool no_more = drained && w_next == w_end;
         unsigned act = __ballot_sync(0xffffffffu, active);
         if (act == 0) {
             if (__any_sync(0xffffffffu, have)) continue;
-            if (exhausted) break;
+            if (no_more) break;
             continue;
         }
+        // (Batching the leaf-triangle tests across lanes - one Moeller-Trumbore round per iteration, or only once N
+        // lanes wait - was measured on B200 and did not pay: the node block then runs with fewer lanes (20 instead of
+        // 26 of 32) and total issued instructions stay within 5 %; profiles/r01c_notes.md.)
         do {
             if (active && trav_step(T, nodes, tris, stack)) active = false, have = true;
             act = __ballot_sync(0xffffffffu, active);
-        } while (act != 0 && (exhausted || __popc(act) >= kRefillBelow));
+        } while (act != 0 && (no_more || __popc(act) >= refill_below));
     }
 }
 
@@ -456,6 +466,9 @@ template <class K> int blocks_per_sm(K kernel, int block) {
 }
 
 } // namespace
+
+cudaError_t set_refill_below(int v) { return cudaMemcpyToSymbol(c_refill_below, &v, sizeof(int)); }
+cudaError_t set_fetch_chunk(int v) { return cudaMemcpyToSymbol(c_fetch_chunk, &v, sizeof(int)); }
 
 cudaError_t launch_selftest(int *d_result, cudaStream_t st) {
     const float a = 1.0f + 1.0f / 4096.0f;

@@ -91,13 +91,20 @@ AKB_HD bool mt_test(v3 o, v3 d, float tmin, float tmax, const float4 &r0, const 
 }
 
 constexpr int kStackSize = 32;
+#ifdef __CUDACC__
+static __constant__ uint32_t c_k47 = 0x47000000u; // opaque to ptxas on purpose, see AKB_Q2F
+#endif
 
 // 32768 + byte j of w, built with one byte permute: the byte lands in mantissa bits 15..8 of 2^15 (0x47000000), so
 // no integer->float conversion (a quarter-rate XU instruction, 48 per node visit) is needed.
+// (The 2^15 pattern is kept in a register the compiler cannot see through, so that the selector is the PRMT's
+// immediate; otherwise ptxas encodes the pattern as the immediate and re-materialises a selector register per plane.)
 #ifdef __CUDA_ARCH__
-#define AKB_Q2F(w, j) __uint_as_float(__byte_perm((w), 0x47000000u, 0x7404u | ((j) << 4)))
+#define AKB_Q2F(w, j) __uint_as_float(__byte_perm((w), k47, 0x7404u | ((j) << 4)))
+#define AKB_Q2F_SETUP() const uint32_t k47 = c_k47
 #else
 #define AKB_Q2F(w, j) akb_u2f(0x47000000u | ((((w) >> (8 * (j))) & 0xFFu) << 8))
+#define AKB_Q2F_SETUP()
 #endif
 
 // Traversal state of one ray. `trav_step` performs one node visit (pop if needed, five 128-bit loads, eight
@@ -108,9 +115,13 @@ struct Trav {
     float idx, idy, idz, tmin, tbest;
     uint32_t oct_inv4;
     uint2 ng;
+    uint32_t tri_base, tmask; // leaf triangles of the last node visit still to be tested
     int sp;
-    bool any;
+    bool any, tri_popped;
     RayHit hit;
+#ifdef AKB_TRAV_STATS
+    uint32_t n_nodes, n_tris, n_child_hits;
+#endif
 };
 
 AKB_HD void trav_init(Trav &T, v3 o, v3 d, float tmin, float tmax, bool any_hit) {
@@ -122,18 +133,32 @@ AKB_HD void trav_init(Trav &T, v3 o, v3 d, float tmin, float tmax, bool any_hit)
     T.oct_inv4 = (7u - ((T.idx < 0 ? 1u : 0u) | (T.idy < 0 ? 2u : 0u) | (T.idz < 0 ? 4u : 0u))) * 0x01010101u;
     T.tmin = tmin, T.tbest = tmax;
     T.ng.x = 0, T.ng.y = 0x80000000u;
+    T.tri_base = 0, T.tmask = 0;
+    T.tri_popped = false;
     T.sp = 0;
     T.any = any_hit;
     T.hit.tri = -1, T.hit.t = INFINITY, T.hit.u = 0.f, T.hit.v = 0.f, T.hit.mat = -1;
 }
 
-// Returns true when the ray is finished (closest: tree exhausted; any-hit: first accepted triangle, hit.tri = 0).
-AKB_HD bool trav_step(Trav &T, const float4 *__restrict__ nodes, const float4 *__restrict__ tris, uint2 *stack) {
+// One node visit: pops a stack entry if the current node group is empty, intersects the eight quantised child boxes
+// and leaves the inner-child hits in T.ng and the leaf-triangle hits in (T.tri_base, T.tmask). A popped entry may also
+// be a postponed triangle group (y <= 0x00FFFFFF), which just becomes the current one. Returns false when there was
+// nothing left to do.
+AKB_HD bool trav_node(Trav &T, const float4 *__restrict__ nodes, uint2 *stack) {
     uint2 ng = T.ng;
     if (ng.y <= 0x00FFFFFFu) {
-        if (T.sp == 0) return true;
+        if (T.sp == 0) return false;
         ng = stack[--T.sp];
+        if (ng.y <= 0x00FFFFFFu) { // postponed triangle group
+            T.tri_base = ng.x, T.tmask = ng.y;
+            T.ng.y = 0;
+            T.tri_popped = true; // must be tested now, not postponed again
+            return true;
+        }
     }
+#ifdef AKB_TRAV_STATS
+    T.n_nodes++;
+#endif
     const uint32_t oct_inv = T.oct_inv4 & 7u;
     const uint32_t imask = ng.y & 0xFFu;
     const int bit = akb_bfind(ng.y);
@@ -154,9 +179,9 @@ AKB_HD bool trav_step(Trav &T, const float4 *__restrict__ nodes, const float4 *_
     const float orgy = fmaf(-32768.0f, adjy, (n0.y - T.o.y) * idy);
     const float orgz = fmaf(-32768.0f, adjz, (n0.z - T.o.z) * idz);
     ng.x = akb_f2u(n1.x);
-    const uint32_t tri_base = akb_f2u(n1.y);
     const float tmin = T.tmin, tbest = T.tbest;
     uint32_t hitmask = 0;
+    AKB_Q2F_SETUP();
 #pragma unroll
     for (int half = 0; half < 2; half++) {
         const uint32_t meta4 = akb_f2u(half ? n1.w : n1.z);
@@ -184,27 +209,46 @@ AKB_HD bool trav_step(Trav &T, const float4 *__restrict__ nodes, const float4 *_
         }
     }
     ng.y = (hitmask & 0xFF000000u) | (ew >> 24);
-    uint32_t tmask = hitmask & 0x00FFFFFFu;
-    while (tmask) {
-        const int j = akb_bfind(tmask);
-        tmask &= ~(1u << j);
-        const float4 *tp = tris + 3 * (size_t)(tri_base + (uint32_t)j);
-        const float4 r0 = AKB_LD4(tp), r1 = AKB_LD4(tp + 1), r2 = AKB_LD4(tp + 2);
-        float t, u, v;
-        if (mt_test(T.o, T.d, T.tmin, T.any ? T.tbest : INFINITY, r0, r1, r2, t, u, v)) {
-            if (T.any) {
-                T.hit.tri = 0;
-                return true;
-            }
-            const int id = (int)akb_f2u(r0.w);
-            if (t < T.tbest || (t == T.tbest && T.hit.tri >= 0 && id < T.hit.tri)) {
-                T.tbest = t;
-                T.hit.t = t, T.hit.u = u, T.hit.v = v, T.hit.tri = id, T.hit.mat = (int)akb_f2u(r1.w);
-            }
+    T.ng = ng;
+    T.tri_base = akb_f2u(n1.y);
+    T.tmask = hitmask & 0x00FFFFFFu;
+    T.tri_popped = false;
+#ifdef AKB_TRAV_STATS
+    T.n_tris += (uint32_t)akb_popc(T.tmask), T.n_child_hits += (uint32_t)akb_popc(hitmask >> 24);
+#endif
+    return true;
+}
+
+// Tests ONE pending leaf triangle (T.tmask != 0). Returns true when an any-hit ray found its occluder.
+AKB_HD bool trav_tri(Trav &T, const float4 *__restrict__ tris) {
+    const int j = akb_bfind(T.tmask);
+    T.tmask &= ~(1u << j);
+    const float4 *tp = tris + 3 * (size_t)(T.tri_base + (uint32_t)j);
+    const float4 r0 = AKB_LD4(tp), r1 = AKB_LD4(tp + 1), r2 = AKB_LD4(tp + 2);
+    float t, u, v;
+    if (mt_test(T.o, T.d, T.tmin, T.any ? T.tbest : INFINITY, r0, r1, r2, t, u, v)) {
+        if (T.any) {
+            T.hit.tri = 0;
+            return true;
+        }
+        const int id = (int)akb_f2u(r0.w);
+        if (t < T.tbest || (t == T.tbest && T.hit.tri >= 0 && id < T.hit.tri)) {
+            T.tbest = t;
+            T.hit.t = t, T.hit.u = u, T.hit.v = v, T.hit.tri = id, T.hit.mat = (int)akb_f2u(r1.w);
         }
     }
-    T.ng = ng;
-    return ng.y <= 0x00FFFFFFu && T.sp == 0;
+    return false;
+}
+
+AKB_HD bool trav_idle(const Trav &T) { return T.ng.y <= 0x00FFFFFFu && T.sp == 0 && T.tmask == 0; }
+
+// One node visit followed by all of its triangle tests. Returns true when the ray is finished (closest: tree
+// exhausted; any-hit: first accepted triangle, hit.tri = 0).
+AKB_HD bool trav_step(Trav &T, const float4 *__restrict__ nodes, const float4 *__restrict__ tris, uint2 *stack) {
+    if (!trav_node(T, nodes, stack)) return true;
+    while (T.tmask)
+        if (trav_tri(T, tris)) return true;
+    return trav_idle(T);
 }
 
 // Run one ray to completion (megakernel, tests/hostcheck).

@@ -5,6 +5,7 @@
 // CPU, so that the `-m "not gpu"` tests can check the host logic (BVH build, quantisation conservativeness,
 // slot map, flattening) and the control flow of the device functions against the oracle without a GPU.
 // libakari_b200.so exports none of this: behind the C ABI there is only the CUDA path.
+#define AKB_TRAV_STATS 1
 #include <atomic>
 #include <string>
 #include <thread>
@@ -175,4 +176,115 @@ extern "C" long hc_trig_mismatches(long n) {
         if (cosf(x) != akb::sincosf_glibc(x, 1)) bad++;
     }
     return bad;
+}
+
+// traversal statistics over a ray batch: out[0] node visits, out[1] triangle tests, out[2] inner-child hits
+extern "C" int hc_trace_stats(void *hv, const float *org, const float *dir, size_t n, int any_hit, double *out) {
+    const SceneDev &S = ((HC *)hv)->dev;
+    double a = 0, b = 0, c = 0;
+    for (size_t i = 0; i < n; i++) {
+        Trav T;
+        uint2 stack[kStackSize];
+        trav_init(T, mk3(org[4 * i], org[4 * i + 1], org[4 * i + 2]), mk3(dir[4 * i], dir[4 * i + 1], dir[4 * i + 2]), org[4 * i + 3],
+                  dir[4 * i + 3], any_hit != 0);
+        T.n_nodes = T.n_tris = T.n_child_hits = 0;
+        while (!trav_step(T, S.nodes, S.tris, stack)) {
+        }
+        a += T.n_nodes, b += T.n_tris, c += T.n_child_hits;
+    }
+    out[0] = a / n, out[1] = b / n, out[2] = c / n;
+    return 0;
+}
+
+// Warp-level cost simulation of traversal scheduling policies (development aid): 32 lanes, rays fetched in order,
+// refill when fewer than `refill` lanes are busy. Costs in issued warp-instructions: node block cn, triangle round ct,
+// refill cf. policy 0: node step then all its triangles; 1: node block (lanes without pending triangles) + one triangle
+// round per iteration; 2: triangle round only when >= th lanes wait (or nobody can do node work); 3: as 2 but lanes
+// with other work postpone their triangle group onto the stack instead of waiting.
+extern "C" double hc_simulate(void *hv, const float *org, const float *dir, size_t n, int any_hit, int policy, int th,
+                              int refill, double cn, double ct, double cf, double *useful_out) {
+    const SceneDev &S = ((HC *)hv)->dev;
+    struct Lane {
+        Trav T;
+        uint2 stack[kStackSize];
+        bool active = false;
+    };
+    std::vector<Lane> L(32);
+    size_t next = 0;
+    double cost = 0, useful = 0;
+    for (;;) {
+        int n_act = 0;
+        for (auto &l : L) n_act += l.active;
+        if (n_act < refill && next < n) {
+            for (auto &l : L)
+                if (!l.active && next < n) {
+                    size_t i = next++;
+                    trav_init(l.T, mk3(org[4 * i], org[4 * i + 1], org[4 * i + 2]), mk3(dir[4 * i], dir[4 * i + 1], dir[4 * i + 2]),
+                              org[4 * i + 3], dir[4 * i + 3], any_hit != 0);
+                    l.active = true;
+                }
+            cost += cf;
+            n_act = 0;
+            for (auto &l : L) n_act += l.active;
+        }
+        if (n_act == 0) break;
+        // node block
+        int n_node = 0;
+        for (auto &l : L) {
+            if (!l.active) continue;
+            if (policy != 0 && l.T.tmask) continue; // waiting for a triangle round
+            if (!trav_node(l.T, S.nodes, l.stack)) {
+                l.active = false;
+                continue;
+            }
+            n_node++;
+        }
+        if (n_node) cost += cn, useful += cn * n_node / 32.0;
+        // triangle rounds
+        auto tri_round = [&](bool only_forced) {
+            int k = 0;
+            for (auto &l : L) {
+                if (!l.active || !l.T.tmask) continue;
+                if (only_forced && !l.T.tri_popped && (l.T.ng.y > 0x00FFFFFFu || l.T.sp > 0) && l.T.sp < kStackSize) continue;
+                k++;
+                if (trav_tri(l.T, S.tris)) l.active = false, l.T.tmask = 0;
+            }
+            if (k) cost += ct, useful += ct * k / 32.0;
+            return k;
+        };
+        auto n_wait = [&]() {
+            int k = 0;
+            for (auto &l : L) k += (l.active && l.T.tmask != 0);
+            return k;
+        };
+        if (policy == 0) {
+            while (n_wait()) tri_round(false);
+        } else if (policy == 1) {
+            tri_round(false);
+        } else if (policy == 2) {
+            if (n_wait() >= th || (n_node == 0 && n_wait() > 0)) tri_round(false);
+        } else {
+            if (n_wait() >= th) {
+                while (n_wait() >= th) tri_round(false);
+            }
+            // postpone or force
+            bool forced = false;
+            for (auto &l : L) {
+                if (!l.active || !l.T.tmask) continue;
+                if (!l.T.tri_popped && (l.T.ng.y > 0x00FFFFFFu || l.T.sp > 0) && l.T.sp < kStackSize) {
+                    uint2 e;
+                    e.x = l.T.tri_base, e.y = l.T.tmask;
+                    // keep node groups above the triangle group: insert below the top? simple: push (processed when popped)
+                    l.stack[l.T.sp++] = e;
+                    l.T.tmask = 0;
+                } else
+                    forced = true;
+            }
+            if (forced) tri_round(true);
+        }
+        for (auto &l : L)
+            if (l.active && trav_idle(l.T)) l.active = false;
+    }
+    if (useful_out) *useful_out = useful / cost;
+    return cost / n;
 }
