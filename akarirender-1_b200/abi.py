@@ -65,7 +65,8 @@ SYMBOLS = ["akb_init", "akb_shutdown", "akb_last_error", "akb_device_count", "ak
 
 
 def lib_path():
-    return os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
+    # AKB_LIB: development override to A/B differently compiled builds of the same library
+    return os.environ.get("AKB_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
 
 
 _lib = None

@@ -23,6 +23,9 @@ namespace akb {
 namespace {
 
 constexpr int kBlock = 128;
+#ifndef AKB_SHADE_MIN_BLOCKS
+#define AKB_SHADE_MIN_BLOCKS 6
+#endif
 constexpr uint32_t kDeadRay = 0x80000000u; // queue-entry flag: path ends at the next shade step, nothing to trace
 
 __device__ __forceinline__ v3 xyz(const float4 &a) { return mk3(a.x, a.y, a.z); }
@@ -355,7 +358,7 @@ __global__ void __launch_bounds__(kBlock) wf_trace_kernel(SceneDev S, RenderConf
 }
 
 template <int SAMP>
-__global__ void __launch_bounds__(kBlock) wf_shade_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
+__global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
     Counters *ctr = ws.ctr;
     // Work list: with material sorting the kNumKeys keyed queues, each padded to a warp so that warps are
     // material-homogeneous; without it the extension queue itself (every traced or parked path gets shaded).
