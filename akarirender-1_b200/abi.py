@@ -61,7 +61,8 @@ LIB_NAME = "libakari_b200.so"
 # every symbol include/akari_b200.h declares (tests check the built library exports all of them)
 SYMBOLS = ["akb_init", "akb_shutdown", "akb_last_error", "akb_device_count", "akb_scene_create", "akb_scene_destroy",
            "akb_scene_info", "akb_render", "akb_render_device", "akb_trace", "akb_trace_device", "akb_generate_rays",
-           "akb_film_to_srgb8"]
+           "akb_film_to_srgb8", "akb_scene_file_load", "akb_scene_file_desc", "akb_scene_file_params",
+           "akb_scene_file_output", "akb_scene_file_destroy", "akb_write_png", "akb_write_pfm"]
 
 
 def lib_path():
@@ -109,5 +110,19 @@ def load():
     L.akb_generate_rays.restype = C.c_int
     L.akb_film_to_srgb8.argtypes = [vp, C.c_int32, C.c_int32, vp]
     L.akb_film_to_srgb8.restype = C.c_int
+    L.akb_scene_file_load.argtypes = [C.c_char_p, C.POINTER(vp)]
+    L.akb_scene_file_load.restype = C.c_int
+    L.akb_scene_file_desc.argtypes = [vp]
+    L.akb_scene_file_desc.restype = C.POINTER(SceneDesc)
+    L.akb_scene_file_params.argtypes = [vp, C.POINTER(RenderParams)]
+    L.akb_scene_file_params.restype = C.c_int
+    L.akb_scene_file_output.argtypes = [vp]
+    L.akb_scene_file_output.restype = C.c_char_p
+    L.akb_scene_file_destroy.argtypes = [vp]
+    L.akb_scene_file_destroy.restype = C.c_int
+    L.akb_write_png.argtypes = [C.c_char_p, vp, C.c_int32, C.c_int32]
+    L.akb_write_png.restype = C.c_int
+    L.akb_write_pfm.argtypes = [C.c_char_p, vp, C.c_int32, C.c_int32]
+    L.akb_write_pfm.restype = C.c_int
     _lib = L
     return L

@@ -42,6 +42,13 @@ akb_status set_err(akb_status st, const char *fmt, ...) {
 
 } // namespace
 
+namespace akb {
+akb_status set_error(akb_status st, const std::string &msg) { // used by host/frontend_api.cpp
+    g_err = msg;
+    return st;
+}
+} // namespace akb
+
 struct akb_scene {
     SceneDev dev;
     std::vector<void *> allocs;

@@ -88,6 +88,20 @@ def _matmul4(a, b):
     return m
 
 
+PI_F = F32(3.1415926535897932384)
+_libm_handle = None
+
+
+def _libm():
+    global _libm_handle
+    if _libm_handle is None:
+        L = C.CDLL("libm.so.6")
+        for f in (L.sinf, L.cosf):
+            f.restype, f.argtypes = C.c_float, [C.c_float]
+        _libm_handle = L
+    return _libm_handle
+
+
 class PerspectiveCamera:
     def __init__(self, fov=80.0, position=(0, 0, 0), rotation=(0, 0, 0), resolution=(512, 512)):
         self.fov = float(fov)  # degrees, as in the scene file
@@ -96,10 +110,11 @@ class PerspectiveCamera:
         self.resolution = (int(resolution[0]), int(resolution[1]))
 
     def c2w(self):
-        rx, ry, rz = (F32(math.radians(F32(r))) for r in self.rotation)
+        # radians(float3) in float (common/math.h:351-354, Pi() is a float literal); sin/cos are glibc's sinf/cosf
+        rx, ry, rz = (F32(F32(F32(r) * PI_F) / F32(180.0)) for r in self.rotation)
 
         def rot(axis, th):
-            s, c = F32(math.sin(th)), F32(math.cos(th))
+            s, c = F32(_libm().sinf(float(th))), F32(_libm().cosf(float(th)))
             m = np.eye(4, dtype=F32)
             if axis == "x":
                 m[1, 1], m[1, 2], m[2, 1], m[2, 2] = c, -s, s, c
@@ -120,7 +135,8 @@ class PerspectiveCamera:
     def desc(self):
         cam = abi.Camera()
         cam.c2w[:] = [float(x) for x in self.c2w().reshape(-1)]
-        cam.fov = float(F32(math.radians(self.fov)))
+        # `fov = radians(value.get<double>())`: double arithmetic with the float-literal Pi, narrowed by the camera ctor
+        cam.fov = float(F32(self.fov * float(PI_F) / 180.0))
         cam.width, cam.height = self.resolution
         cam.lens_radius = 0.0
         cam.focal_distance = 0.0
@@ -219,6 +235,128 @@ class AO:
         p.ao_occlude = self.occlude
         p.rank, p.world_size, p.tile_size = rank, world_size, shard_tile
         return p
+
+
+# ---- `.akari` text (core/parser.cpp) --------------------------------------------------
+def sdl_number(v):
+    """Shortest fixed-point literal (the SDL has no exponent syntax) that the reference's number reader
+    (core/parser.cpp:338-363: n + frac / 10^k in double, then narrowed) maps back to float32(v)."""
+    f = F32(v)
+    if not np.isfinite(f):
+        raise ValueError("the scene language cannot express %r" % (v,))
+    for prec in range(1, 60):
+        t = np.format_float_positional(f, precision=prec, unique=False, fractional=False, trim="-")
+        neg, body = t.startswith("-"), t.lstrip("-")
+        ip, _, fp = body.partition(".")
+        if len(ip.lstrip("0")) + len(fp.lstrip("0")) > 18:
+            break
+        val = float(int(ip)) + (float(int(fp)) / float(10 ** len(fp)) if fp else 0.0)
+        if F32(-val if neg else val) == f:
+            return t
+    raise ValueError("no exact literal for %r" % (v,))
+
+
+def _sdl_list(vals):
+    return "[" + ", ".join(sdl_number(x) for x in vals) + "]"
+
+
+def write_akari(scene, directory, name="scene.akari"):
+    """Writes `scene` as a reference-format scene file + one .mesh per shape into `directory`. Returns the path."""
+    import os
+    os.makedirs(directory, exist_ok=True)
+    lines, names = [], {}
+
+    def material(m):
+        if id(m) in names:
+            return names[id(m)]
+        if isinstance(m, MixMaterial):
+            a, b = material(m.first), material(m.second)
+            body = "MixMaterial { fraction: %s, first: $%s, second: $%s }" % (sdl_number(m.fraction), a, b)
+        elif isinstance(m, DiffuseMaterial):
+            body = "DiffuseMaterial { color: %s }" % _sdl_list(m.color)
+        elif isinstance(m, GlossyMaterial):
+            body = "GlossyMaterial { color: %s, roughness: %s }" % (_sdl_list(m.color), sdl_number(m.roughness))
+        elif isinstance(m, EmissiveMaterial):
+            body = "EmissiveMaterial { color: %s }" % _sdl_list(m.color)
+        elif isinstance(m, DielectricMaterial):
+            body = "DielectricMaterial { color: %s, ior: %s }" % (_sdl_list(m.color), sdl_number(m.ior))
+        else:
+            raise TypeError(m)
+        names[id(m)] = "mat%d" % len(names)
+        lines.append("export %s = %s" % (names[id(m)], body))
+        return names[id(m)]
+
+    shape_names = []
+    for k, sh in enumerate(scene.shapes):
+        write_mesh(os.path.join(directory, "shape%d.mesh" % k), sh)
+        mats = ", ".join("$" + material(m) for m in sh.materials)
+        lines.append("export shape%d = AkariMesh {\n  path: \"shape%d.mesh\",\n  materials: [%s]\n}" % (k, k, mats))
+        shape_names.append("$shape%d" % k)
+    cam = scene.camera
+    lines.append("export camera = PerspectiveCamera {\n  fov: %s,\n  position: %s,\n  rotation: %s,\n  resolution: [%d, %d]\n}"
+                 % (sdl_number(cam.fov), _sdl_list(cam.position), _sdl_list(cam.rotation), cam.resolution[0],
+                    cam.resolution[1]))
+    it = scene.integrator
+    if isinstance(it, AO):
+        integ = "AO { spp: %d%s }" % (it.spp, "" if math.isinf(it.occlude) else ", occlude: " + sdl_number(it.occlude))
+    else:
+        integ = ("Path { spp: %d, max_depth: %d, tile_size: %d, ray_clamp: %s, wavefront: %s"
+                 % (it.spp, it.max_depth, it.tile_size, sdl_number(it.ray_clamp), "true" if it.wavefront else "false"))
+        if it.rr_start_depth:
+            integ += ", rr_start_depth: %d" % it.rr_start_depth
+        if it.sampler == "pcg":
+            integ += ", sampler: \"pcg\""
+        if it.sort_materials:
+            integ += ", sort_materials: true"
+        integ += " }"
+    lines.append("// written by akarirender-1_b200.nodes.write_akari\nexport scene = Scene {\n  camera: $camera,\n  integrator: %s,\n"
+                 "  output: \"%s\",\n  shapes: [%s]\n}" % (integ, scene.output, ", ".join(shape_names)))
+    path = os.path.join(directory, name)
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    return path
+
+
+class SceneFile:
+    """A scene parsed by the C++ front-end (akb_scene_file_*): the `akari scene.akari` entry of the reference
+    (cmd/akari.cpp:78-92). Quacks like `Scene` for `Backend` (flatten / camera.resolution / integrator.params)."""
+
+    def __init__(self, path):
+        self.lib = abi.load()
+        h = C.c_void_p()
+        if self.lib.akb_scene_file_load(str(path).encode(), C.byref(h)) != abi.OK:
+            raise RuntimeError(self.lib.akb_last_error().decode(errors="replace"))
+        self.h = h
+        self.desc = self.lib.akb_scene_file_desc(h).contents
+        self.output = self.lib.akb_scene_file_output(h).decode()
+        self.camera = self
+        self.integrator = self
+        self.resolution = (self.desc.camera.width, self.desc.camera.height)
+
+    def params(self, rank=0, world_size=1, shard_tile=32):
+        p = abi.RenderParams()
+        if self.lib.akb_scene_file_params(self.h, C.byref(p)) != abi.OK:
+            raise RuntimeError(self.lib.akb_last_error().decode(errors="replace"))
+        p.rank, p.world_size, p.tile_size = rank, world_size, shard_tile
+        return p
+
+    @property
+    def spp(self):
+        return self.params().spp
+
+    def flatten(self):
+        return self.desc, [self]
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.akb_scene_file_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 # ---- scene (core/nodes/scene.cpp:96-165) --------------------------------------------------------------------

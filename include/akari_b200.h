@@ -189,6 +189,29 @@ akb_status akb_generate_rays(akb_scene *scene, const int32_t *xy, const float *u
  * sRGB OETF -> round(255.5*x) clamp -> RGB8. HOST pointers; runs on the device. */
 akb_status akb_film_to_srgb8(const float *rgbw, int32_t width, int32_t height, uint8_t *out_rgb8);
 
+/* ---- scene files (front-end) ------------------------------------------------------------------------ */
+
+/* Replaces SceneGraphParser<C>::parse_file + the scene-graph nodes' object_field/compile for the Path hot path
+ * (core/parser.cpp:150-363, core/nodes/{scene,camera,mesh,material,integrator}.cpp, core/mesh.cpp:48-85;
+ * cmd/akari.cpp:78-92 looks up the export `scene`): reads a `.akari` file with its imports and `.mesh` files and
+ * flattens it. Host-only (no device needed). The returned description and everything it points to belong to the
+ * handle and stay valid until akb_scene_file_destroy; hand it to akb_scene_create, which deep-copies. */
+typedef struct akb_scene_file akb_scene_file; /* opaque */
+akb_status akb_scene_file_load(const char *path, akb_scene_file **out_file);
+const akb_scene_desc *akb_scene_file_desc(const akb_scene_file *file);
+/* Integrator node -> parameters (PathIntegratorNode / AOIntegratorNode defaults, core/nodes/integrator.cpp:26-84;
+ * rank 0 of 1). */
+akb_status akb_scene_file_params(const akb_scene_file *file, akb_render_params *out_params);
+/* Scene.output (core/nodes/scene.cpp:100-101), default "out.png". */
+const char *akb_scene_file_output(const akb_scene_file *file);
+akb_status akb_scene_file_destroy(akb_scene_file *file);
+
+/* Replaces the image write at the end of Film::write_image (core/film.h:97-113 -> core/image.cpp:38-61): 8-bit RGB
+ * rows, top to bottom, as PNG. Host-only. */
+akb_status akb_write_png(const char *path, const uint8_t *rgb8, int32_t width, int32_t height);
+/* Float output the reference lacks: radiance/weight per pixel as a little-endian RGB .pfm. Host-only. */
+akb_status akb_write_pfm(const char *path, const float *rgbw, int32_t width, int32_t height);
+
 #ifdef __cplusplus
 }
 #endif
