@@ -249,7 +249,8 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
     akb_status st = check_ready("akb_render_device");
     if (st != AKB_OK) return st;
     if (!sc || !p || !d_out_rgbw) return set_err(AKB_INVALID_ARG, "akb_render_device: null argument");
-    if (p->integrator != AKB_INTEGRATOR_PATH) return set_err(AKB_INVALID_ARG, "akb_render_device: only the Path integrator is implemented");
+    if (p->integrator != AKB_INTEGRATOR_PATH && p->integrator != AKB_INTEGRATOR_AO) return set_err(AKB_INVALID_ARG, "akb_render_device: unknown integrator %d", p->integrator);
+    if (p->integrator == AKB_INTEGRATOR_AO && !(p->ao_occlude > 0.0f)) return set_err(AKB_INVALID_ARG, "akb_render_device: AO.occlude must be positive");
     if (p->spp < 0 || p->max_depth < 0) return set_err(AKB_INVALID_ARG, "akb_render_device: negative spp/max_depth");
     if (p->sampler != AKB_SAMPLER_LCG && p->sampler != AKB_SAMPLER_PCG) return set_err(AKB_INVALID_ARG, "akb_render_device: bad sampler");
     const int world = p->world_size > 0 ? p->world_size : 1;
@@ -267,7 +268,10 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
     CU(cudaMemsetAsync(d_out_rgbw, 0, n_px * sizeof(float4), stream));
     CU(cudaMemsetAsync(sc->d_ctr, 0, sizeof(Counters), stream));
     CU(cudaEventRecord(sc->ev0, stream));
-    if (p->mode == AKB_MODE_MEGAKERNEL) {
+    if (p->integrator == AKB_INTEGRATOR_AO) {
+        CU(launch_ao(sc->dev, rc, p->ao_occlude, (float4 *)d_out_rgbw, sc->d_ctr, stream));
+        launches = 1;
+    } else if (p->mode == AKB_MODE_MEGAKERNEL) {
         CU(launch_megakernel(sc->dev, rc, (float4 *)d_out_rgbw, sc->d_ctr, stream));
         launches = 1;
     } else {

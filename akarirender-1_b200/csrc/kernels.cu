@@ -238,6 +238,52 @@ __global__ void __launch_bounds__(kBlock) megakernel(SceneDev S, RenderConfig rc
     }
 }
 
+// AO integrator (`AO { spp, occlude }`, core/nodes/integrator.cpp:26-49): one thread per owned pixel runs the sample loop
+// of AmbientOcclusion::render (kernel/integrators/cpu/integrator.cpp:72-80): camera ray -> closest hit -> one cosine ray.
+// Film semantics are the CPU integrator's (add_sample(L, 1) per sample), like the Path integrator's.
+template <int SAMP>
+__global__ void __launch_bounds__(kBlock) ao_kernel(SceneDev S, RenderConfig rc, float occlude, float4 *__restrict__ film,
+                                                    Counters *ctr) {
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    int x = 0, y = 0;
+    const bool valid = slot < rc.map.n_slots() && slot_to_pixel(rc.map, slot, x, y);
+    unsigned long long n_closest = 0, n_shadow = 0, n_samples = 0;
+    if (valid) {
+        Rng<SAMP> rng;
+        rng.set_sample_index((uint64_t)(x + y * rc.map.width));
+        float sum = 0, weight = 0;
+        for (int s = 0; s < rc.spp; s++) {
+            float u1x, u1y, u2x, u2y;
+            rng.next2d(u2x, u2y);
+            rng.next2d(u1x, u1y);
+            v3 o, d;
+            camera_generate_ray(S.cam, u2x, u2y, x, y, o, d);
+            RayHit hit, dummy;
+            float L = 0.0f;
+            n_closest++;
+            if (traverse8<false>(S.nodes, S.tris, o, d, AKB_EPS, INFINITY, hit)) {
+                const RaySeg r = ao_ray<SAMP>(S, rng, hit.u, hit.v, hit.tri, occlude);
+                n_shadow++;
+                L = traverse8<true>(S.nodes, S.tris, r.o, r.d, r.tmin, r.tmax, dummy) ? 0.0f : 1.0f;
+            }
+            weight += 1.0f;
+            sum += L;
+            n_samples++;
+        }
+        film[(size_t)y * rc.map.width + x] = make_float4(sum, sum, sum, weight);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        n_closest += __shfl_down_sync(0xffffffffu, n_closest, o);
+        n_shadow += __shfl_down_sync(0xffffffffu, n_shadow, o);
+        n_samples += __shfl_down_sync(0xffffffffu, n_samples, o);
+    }
+    if ((threadIdx.x & 31) == 0 && n_samples) {
+        atomicAdd(&ctr->stat_closest, n_closest);
+        atomicAdd(&ctr->stat_shadow, n_shadow);
+        atomicAdd(&ctr->stat_samples, n_samples);
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 // Wavefront kernels.
 
@@ -513,6 +559,17 @@ cudaError_t launch_megakernel(const SceneDev &S, const RenderConfig &rc, float4 
         megakernel<AKB_SAMPLER_PCG><<<grid, kBlock, 0, st>>>(S, rc, film, ctr);
     else
         megakernel<AKB_SAMPLER_LCG><<<grid, kBlock, 0, st>>>(S, rc, film, ctr);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ao(const SceneDev &S, const RenderConfig &rc, float occlude, float4 *film, Counters *ctr, cudaStream_t st) {
+    const int n = rc.map.n_slots();
+    if (n == 0) return cudaSuccess;
+    const int grid = (n + kBlock - 1) / kBlock;
+    if (rc.sampler == AKB_SAMPLER_PCG)
+        ao_kernel<AKB_SAMPLER_PCG><<<grid, kBlock, 0, st>>>(S, rc, occlude, film, ctr);
+    else
+        ao_kernel<AKB_SAMPLER_LCG><<<grid, kBlock, 0, st>>>(S, rc, occlude, film, ctr);
     return cudaGetLastError();
 }
 

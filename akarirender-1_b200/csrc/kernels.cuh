@@ -53,6 +53,8 @@ cudaError_t launch_generate_rays(const SceneDev &S, const int32_t *xy, const flo
 cudaError_t launch_film_to_srgb8(const float4 *rgbw, size_t n, uint8_t *out, cudaStream_t st);
 cudaError_t launch_megakernel(const SceneDev &S, const RenderConfig &rc, float4 *film, Counters *ctr, cudaStream_t st);
 
+cudaError_t launch_ao(const SceneDev &S, const RenderConfig &rc, float occlude, float4 *film, Counters *ctr, cudaStream_t st);
+
 cudaError_t launch_wf_init(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int n_sms, cudaStream_t st);
 cudaError_t launch_wf_trace(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int parity, int n_sms,
                             cudaStream_t st);

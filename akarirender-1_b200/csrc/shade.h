@@ -492,4 +492,21 @@ AKB_HD v3 clamp_sample(v3 L, float ray_clamp) {
     return L;
 }
 
+// The secondary ray of AmbientOcclusion's Li (kernel/integrators/cpu/integrator.cpp:46-51,
+// gpu/cuda/integrator.cpp:49-54): Frame3f(trig.ng()), one cosine-weighted direction, origin trig.p(uv), Ray ctor
+// defaults (tmin = Eps, tmax = inf). "closest hit nearer than `occlude`" is asked as an any-hit query with tmax = occlude.
+template <int SAMP> AKB_HD RaySeg ao_ray(const SceneDev &S, Rng<SAMP> &rng, float hu, float hv, int tri, float occlude) {
+    const float4 *sr = S.shading + 6 * (size_t)tri;
+    const float4 s0 = AKB_LD4(sr), s1 = AKB_LD4(sr + 1), s2 = AKB_LD4(sr + 2);
+    const v3 ng = mk3(s1.w, s2.w, AKB_LD4(sr + 3).w);
+    const Frame fr = frame_make(ng);
+    float ux, uy;
+    rng.next2d(ux, uy);
+    RaySeg r;
+    r.d = l2w(fr, cosine_hemisphere(ux, uy));
+    r.o = lerp3(mk3(s0.x, s0.y, s0.z), mk3(s1.x, s1.y, s1.z), mk3(s2.x, s2.y, s2.z), hu, hv);
+    r.tmin = AKB_EPS, r.tmax = occlude;
+    return r;
+}
+
 } // namespace akb

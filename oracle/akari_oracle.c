@@ -583,6 +583,31 @@ static void run_path(const oracle_scene *s, path_t *pt, int px, int py, int rr_s
     }
 }
 
+/* AmbientOcclusion::render's Li (kernel/integrators/cpu/integrator.cpp:42-60): primary hit -> one cosine-weighted ray
+ * about the geometric normal from trig.p(uv) (Ray defaults tmin = Eps, tmax = inf); 0 if its closest hit is nearer
+ * than `occlude`, else 1; a primary miss gives 0. Returns the grey value; *n_rays counts Scene::intersect calls. */
+static float run_ao(const oracle_scene *s, sampler_t *smp, int px, int py, float occlude, uint64_t *n_rays) {
+    float u1x, u1y, u2x, u2y;
+    next2d(smp, &u2x, &u2y); /* right-to-left argument evaluation, as in run_path */
+    next2d(smp, &u1x, &u1y);
+    (void)u1x; (void)u1y;
+    ray_t ray = camera_generate_ray(&s->cam, u2x, u2y, px, py);
+    float t, hu, hv;
+    (*n_rays)++;
+    int64_t ti = scene_intersect(s, &ray, &t, &hu, &hv);
+    if (ti < 0) return 0.0f;
+    const tri_t *tr = &s->tris[ti];
+    v3 ng = normalize3(cross3(sub3(tr->v[1], tr->v[0]), sub3(tr->v[2], tr->v[0])));
+    frame_t fr = frame_make(ng);
+    float ux, uy;
+    next2d(smp, &ux, &uy);
+    v3 w = l2w(&fr, cosine_hemisphere(ux, uy));
+    ray_t r2; r2.o = lerp3v(tr->v[0], tr->v[1], tr->v[2], hu, hv); r2.d = w; r2.tmin = K_EPS; r2.tmax = INFINITY;
+    (*n_rays)++;
+    if (scene_intersect(s, &r2, &t, &hu, &hv) >= 0 && t < occlude) return 0.0f;
+    return 1.0f;
+}
+
 /* ---- scene construction: SceneNode::compile (core/nodes/scene.cpp:43-95) --------------------------------- */
 static v3 ld3(const float *p) { return mk3(p[0], p[1], p[2]); }
 
@@ -710,6 +735,12 @@ static void *render_worker(void *arg) {
             sampler_set_index(&smp, (uint64_t)(x + (int)y * W));
             v3 sum = {0, 0, 0}; float weight = 0;
             for (int sidx = 0; sidx < p->spp; sidx++) {
+                if (p->integrator == AKB_INTEGRATOR_AO) { /* cpu/integrator.cpp:72-80 */
+                    float g = run_ao(j->s, &smp, x, (int)y, p->ao_occlude, &c1);
+                    weight += 1.0f; sum = add3(sum, mk3(g, g, g));
+                    c0++;
+                    continue;
+                }
                 path_t pt; memset(&pt, 0, sizeof pt);
                 pt.beta = mk3(1, 1, 1); pt.max_depth = p->max_depth; pt.smp = smp;
                 run_path(j->s, &pt, x, (int)y, p->rr_start_depth);
@@ -754,7 +785,7 @@ int akor_trace(const oracle_scene *s, const float *org_tmin, const float *dir_tm
 /* counts (may be NULL): [0] samples, [1] closest-hit rays, [2] shadow rays */
 int akor_render(const oracle_scene *s, const akb_render_params *p, int x0, int y0, int x1, int y1, float *out_rgbw,
                 int n_threads, uint64_t *counts) {
-    if (p->integrator != AKB_INTEGRATOR_PATH) return 1;
+    if (p->integrator != AKB_INTEGRATOR_PATH && p->integrator != AKB_INTEGRATOR_AO) return 1;
     job_t j; memset(&j, 0, sizeof j);
     j.s = s; j.p = p; j.x0 = x0; j.y0 = y0; j.x1 = x1; j.y1 = y1; j.out = out_rgbw; j.next = y0;
     run_threads(render_worker, &j, n_threads);

@@ -259,10 +259,30 @@ int akref_render(void *h, const akb_render_params *p, int x0, int y0, int x1, in
                  int n_threads) {
     AKR_IMPORT_TYPES()
     auto *rs = (RefScene *)h;
-    if (p->integrator != AKB_INTEGRATOR_PATH || p->rr_start_depth != 0 || p->ray_clamp != 0.0f) {
-        g_err = "reference CPU path has no AO-through-this-entry/RR/clamp";
+    const bool ao = p->integrator == AKB_INTEGRATOR_AO;
+    if ((!ao && p->integrator != AKB_INTEGRATOR_PATH) || p->rr_start_depth != 0 || p->ray_clamp != 0.0f) {
+        g_err = "reference CPU path has no RR/clamp";
         return 1;
     }
+    const Float occlude = p->ao_occlude;
+    // The body of the `Li` lambda of cpu::AmbientOcclusion::render (kernel/integrators/cpu/integrator.cpp:42-60), which
+    // is local to that function (and that file needs Film/thread-pool code this harness does not link): the same calls
+    // on the reference's own Scene, Triangle, Frame3f and sampling<C>, in the same order.
+    auto ao_li = [&](Ray3f ray, Sampler<C> &sampler) -> Spectrum {
+        Intersection<C> intersection;
+        if (rs->scene.intersect(ray, &intersection)) {
+            auto trig = rs->scene.get_triangle(intersection.geom_id, intersection.prim_id);
+            Frame3f frame(trig.ng());
+            auto w = sampling<C>::cosine_hemisphere_sampling(sampler.next2d());
+            w = frame.local_to_world(w);
+            ray = Ray3f(trig.p(intersection.uv), w);
+            intersection = Intersection<C>();
+            if (rs->scene.intersect(ray, &intersection) && intersection.t < occlude)
+                return Spectrum(0);
+            return Spectrum(1);
+        }
+        return Spectrum(0);
+    };
     Scene<C> &scene = rs->scene;
     if (p->sampler == AKB_SAMPLER_PCG)
         scene.sampler = PCGSampler<C>();
@@ -286,6 +306,13 @@ int akref_render(void *h, const akb_render_params *p, int x0, int y0, int x1, in
                 Float weight = 0;
                 for (int s = 0; s < spp; s++) {
                     sampler.start_next_sample();
+                    if (ao) { // cpu/integrator.cpp:72-80
+                        CameraSample<C> sample = camera.generate_ray(sampler.next2d(), sampler.next2d(), int2(x, y));
+                        auto L = ao_li(sample.ray, sampler);
+                        weight += 1.0f;
+                        sum += L;
+                        continue;
+                    }
                     GenericPathTracer<C> pt;
                     pt.depth = 0;
                     pt.max_depth = max_depth;

@@ -49,6 +49,22 @@ template <int SAMP> void render_rows(HC *h, const akb_render_params *p, float *o
             v3 sum = mk3(0, 0, 0);
             float weight = 0;
             for (int s = 0; s < p->spp; s++) {
+                if (p->integrator == AKB_INTEGRATOR_AO) { // the body of ao_kernel (csrc/kernels.cu)
+                    float u1x, u1y, u2x, u2y;
+                    rng.next2d(u2x, u2y);
+                    rng.next2d(u1x, u1y);
+                    v3 o, d;
+                    camera_generate_ray(S.cam, u2x, u2y, x, y, o, d);
+                    RayHit hit, dummy;
+                    float L = 0.0f;
+                    if (traverse8<false>(S.nodes, S.tris, o, d, AKB_EPS, INFINITY, hit)) {
+                        const RaySeg r = ao_ray<SAMP>(S, rng, hit.u, hit.v, hit.tri, p->ao_occlude);
+                        L = traverse8<true>(S.nodes, S.tris, r.o, r.d, r.tmin, r.tmax, dummy) ? 0.0f : 1.0f;
+                    }
+                    weight += 1.0f;
+                    sum = add3(sum, mk3(L, L, L));
+                    continue;
+                }
                 PathState<SAMP> ps;
                 ps.L = mk3(0, 0, 0), ps.beta = mk3(1, 1, 1), ps.depth = 0, ps.rng = rng;
                 float u1x, u1y, u2x, u2y;
