@@ -6,13 +6,14 @@ built: there is no CPU fallback on the product path.
 import ctypes as C
 import os
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 OK, INVALID_ARG, CUDA_ERROR, NCCL_ERROR, OOM, NO_DEVICE = range(6)
 MAT_DIFFUSE, MAT_GLOSSY, MAT_EMISSIVE, MAT_MIX, MAT_DIELECTRIC = range(5)
 INTEGRATOR_PATH, INTEGRATOR_AO = 0, 1
 SAMPLER_LCG, SAMPLER_PCG = 0, 1
 MODE_WAVEFRONT, MODE_MEGAKERNEL = 0, 1
+SPLIT_TILE, SPLIT_SAMPLE = 0, 1
 
 
 class Material(C.Structure):
@@ -43,7 +44,7 @@ class RenderParams(C.Structure):
     _fields_ = [("integrator", C.c_int32), ("spp", C.c_int32), ("max_depth", C.c_int32), ("ray_clamp", C.c_float),
                 ("sampler", C.c_int32), ("rr_start_depth", C.c_int32), ("mode", C.c_int32),
                 ("sort_materials", C.c_int32), ("ao_occlude", C.c_float), ("rank", C.c_int32),
-                ("world_size", C.c_int32), ("tile_size", C.c_int32)]
+                ("world_size", C.c_int32), ("tile_size", C.c_int32), ("split", C.c_int32)]
 
 
 class RenderStats(C.Structure):

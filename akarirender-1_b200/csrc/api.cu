@@ -259,9 +259,12 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
     if ((tile & (tile - 1)) != 0 || tile < 8 || tile > 1024) return set_err(AKB_INVALID_ARG, "akb_render_device: tile_size must be a power of two in [8,1024]");
     cudaStream_t stream = (cudaStream_t)cuda_stream;
     RenderConfig rc;
-    rc.spp = p->spp, rc.max_depth = p->max_depth, rc.rr_start = p->rr_start_depth, rc.sampler = p->sampler;
+    if (p->split != AKB_SPLIT_TILE && p->split != AKB_SPLIT_SAMPLE) return set_err(AKB_INVALID_ARG, "akb_render_device: bad split %d", p->split);
+    const Shard shard = make_shard(sc->width, sc->height, p);
+    rc.spp = shard.spp, rc.max_depth = p->max_depth, rc.rr_start = p->rr_start_depth, rc.sampler = p->sampler;
     rc.sort_materials = p->sort_materials, rc.ray_clamp = p->ray_clamp;
-    rc.map = make_slot_map(sc->width, sc->height, tile, p->rank, world);
+    rc.seed_offset = shard.seed_offset;
+    rc.map = shard.map;
     const size_t n_px = (size_t)sc->width * sc->height;
     uint64_t launches = 0;
     std::vector<cudaEvent_t> evs;

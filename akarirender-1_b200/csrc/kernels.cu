@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(kBlock) megakernel(SceneDev S, RenderConfig rc
     unsigned long long n_closest = 0, n_shadow = 0, n_samples = 0;
     if (valid) {
         Rng<SAMP> rng;
-        rng.set_sample_index((uint64_t)(x + y * rc.map.width));
+        rng.set_sample_index((uint64_t)(x + y * rc.map.width) + rc.seed_offset);
         v3 sum = mk3(0, 0, 0);
         float weight = 0;
         for (int s = 0; s < rc.spp; s++) {
@@ -250,7 +250,7 @@ __global__ void __launch_bounds__(kBlock) ao_kernel(SceneDev S, RenderConfig rc,
     unsigned long long n_closest = 0, n_shadow = 0, n_samples = 0;
     if (valid) {
         Rng<SAMP> rng;
-        rng.set_sample_index((uint64_t)(x + y * rc.map.width));
+        rng.set_sample_index((uint64_t)(x + y * rc.map.width) + rc.seed_offset);
         float sum = 0, weight = 0;
         for (int s = 0; s < rc.spp; s++) {
             float u1x, u1y, u2x, u2y;
@@ -313,7 +313,7 @@ template <int SAMP> __global__ void __launch_bounds__(256) wf_init_kernel(SceneD
         if (slot < n) ws.acc[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (valid) {
             Rng<SAMP> rng;
-            rng.set_sample_index((uint64_t)(x + y * rc.map.width));
+            rng.set_sample_index((uint64_t)(x + y * rc.map.width) + rc.seed_offset);
             start_sample<SAMP>(S, ws, slot, x, y, rng, 0);
         }
         queue_push(valid, (uint32_t)slot, ws.q_ext[0], &ws.ctr->n_ext[0]);

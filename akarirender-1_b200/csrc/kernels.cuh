@@ -36,6 +36,7 @@ struct Workspace {
 struct RenderConfig {
     int spp, max_depth, rr_start, sampler, sort_materials;
     float ray_clamp;
+    unsigned long long seed_offset; // added to the per-pixel sampler seed x + y*W (AKB_SPLIT_SAMPLE)
     SlotMap map;
 };
 

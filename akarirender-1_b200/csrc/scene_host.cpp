@@ -212,4 +212,20 @@ SlotMap make_slot_map(int width, int height, int tile, int rank, int world) {
     return m;
 }
 
+Shard make_shard(int width, int height, const akb_render_params *p) {
+    const int world = p->world_size > 0 ? p->world_size : 1;
+    const int tile = p->tile_size > 0 ? p->tile_size : 32;
+    Shard s;
+    if (p->split == AKB_SPLIT_SAMPLE) {
+        s.map = make_slot_map(width, height, tile, 0, 1);
+        s.spp = p->spp / world + (p->rank < p->spp % world ? 1 : 0);
+        s.seed_offset = (uint64_t)p->rank * (uint64_t)width * (uint64_t)height;
+    } else {
+        s.map = make_slot_map(width, height, tile, p->rank, world);
+        s.spp = p->spp;
+        s.seed_offset = 0;
+    }
+    return s;
+}
+
 } // namespace akb

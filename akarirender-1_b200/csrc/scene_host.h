@@ -42,6 +42,15 @@ struct SlotMap {
 };
 SlotMap make_slot_map(int width, int height, int tile, int rank, int world);
 
+// This rank's share of a frame (akb_split, include/akari_b200.h): which pixels, how many samples of each, and the
+// offset added to the per-pixel sampler seed x + y*W.
+struct Shard {
+    SlotMap map;
+    int spp;
+    uint64_t seed_offset;
+};
+Shard make_shard(int width, int height, const akb_render_params *p);
+
 AKB_HD uint32_t morton_compact(uint32_t v) { // even bits of v -> low half
     v &= 0x55555555u;
     v = (v | (v >> 1)) & 0x33333333u;

@@ -30,11 +30,12 @@ def combine_film(film, dst=0, group=None):
     return film
 
 
-def render_sharded(backend, film, rank, world, shard_tile=32, params=None, stream=0):
-    """Render this rank's tiles into `film` (a CUDA float32 tensor of H*W*4) and combine on rank 0."""
+def render_sharded(backend, film, rank, world, shard_tile=32, params=None, stream=0, split=0):
+    """Render this rank's share (split 0: interleaved tiles, 1: a share of every pixel's samples; akb_split) into
+    `film` (a CUDA float32 tensor of H*W*4) and combine on rank 0. Either way the combine is one sum-reduce."""
     p = params if params is not None else backend.scene.integrator.params(rank=rank, world_size=world,
                                                                           shard_tile=shard_tile)
-    p.rank, p.world_size, p.tile_size = rank, world, shard_tile
+    p.rank, p.world_size, p.tile_size, p.split = rank, world, shard_tile, split
     stats = backend.render_device(film.data_ptr(), p, stream)
     combine_film(film)
     return stats

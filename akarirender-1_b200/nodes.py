@@ -210,8 +210,9 @@ class Path:
         self.wavefront = bool(wavefront) and not megakernel
         self.sampler, self.rr_start_depth, self.sort_materials = sampler, int(rr_start_depth), bool(sort_materials)
 
-    def params(self, rank=0, world_size=1, shard_tile=32):
+    def params(self, rank=0, world_size=1, shard_tile=32, split=abi.SPLIT_TILE):
         p = abi.RenderParams()
+        p.split = split
         p.integrator = abi.INTEGRATOR_PATH
         p.spp, p.max_depth, p.ray_clamp = self.spp, self.max_depth, self.ray_clamp
         p.sampler = abi.SAMPLER_PCG if self.sampler == "pcg" else abi.SAMPLER_LCG
@@ -227,8 +228,9 @@ class AO:
     def __init__(self, spp=16, occlude=float("inf")):
         self.spp, self.occlude = int(spp), float(occlude)
 
-    def params(self, rank=0, world_size=1, shard_tile=32):
+    def params(self, rank=0, world_size=1, shard_tile=32, split=abi.SPLIT_TILE):
         p = abi.RenderParams()
+        p.split = split
         p.integrator = abi.INTEGRATOR_AO
         p.spp, p.max_depth, p.ray_clamp = self.spp, 0, 0.0
         p.sampler, p.rr_start_depth, p.mode, p.sort_materials = abi.SAMPLER_LCG, 0, abi.MODE_MEGAKERNEL, 0
@@ -333,11 +335,11 @@ class SceneFile:
         self.integrator = self
         self.resolution = (self.desc.camera.width, self.desc.camera.height)
 
-    def params(self, rank=0, world_size=1, shard_tile=32):
+    def params(self, rank=0, world_size=1, shard_tile=32, split=abi.SPLIT_TILE):
         p = abi.RenderParams()
         if self.lib.akb_scene_file_params(self.h, C.byref(p)) != abi.OK:
             raise RuntimeError(self.lib.akb_last_error().decode(errors="replace"))
-        p.rank, p.world_size, p.tile_size = rank, world_size, shard_tile
+        p.rank, p.world_size, p.tile_size, p.split = rank, world_size, shard_tile, split
         return p
 
     @property

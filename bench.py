@@ -48,6 +48,9 @@ def make_scene(pkg, workload, spp, ref_subset=False):
     elif workload == "c1":
         sc = s.cornell_box((512, 512), spp or 16, 5)
         name = "C1: Cornell box 512x512, %d spp, Path max_depth 5" % sc.integrator.spp
+    elif workload == "c4":
+        sc = s.instanced_scene(n=708, resolution=(3840, 2160), spp=spp or 256, max_depth=8)
+        name = "C4: 10 placed copies of the 999700-triangle terrain (9997000 triangles, 10 meshes), 3840x2160, %d spp, Path max_depth 8, 70%% Diffuse / 30%% GGX(0.3)" % sc.integrator.spp
     elif workload == "c5":
         sc = s.many_light_scene(n=708, resolution=(1920, 1080), spp=spp or 128, max_depth=16, n_quads=5000,
                                 rr_start_depth=0 if ref_subset else 3)
@@ -130,7 +133,10 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c3", choices=["c3", "c1", "c5"])
+    ap.add_argument("--workload", default="c3", choices=["c3", "c1", "c5", "c4", "c2"])
+    ap.add_argument("--split", default="auto", choices=["auto", "tile", "sample"],
+                    help="N>1: how ranks share the frame (akb_split). auto = sample split (every GPU keeps a full-size "
+                         "wavefront; statistically equivalent film), with the bit-identical tile split timed beside it")
     ap.add_argument("--spp", type=int, default=0)
     ap.add_argument("--mode", default="wavefront", choices=["wavefront", "megakernel"])
     ap.add_argument("--cpu-rows", type=int, default=24)
@@ -139,6 +145,14 @@ def main():
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     pkg = importlib.import_module("akarirender-1_b200")
+    # Libraries (NCCL's version banner, the reference's logger) write to fd 1; the contract is ONE JSON line on stdout.
+    # Everything but that line goes to stderr.
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
 
     if a.impl == "reference":
         if rank != 0:
@@ -151,7 +165,7 @@ def main():
                 "cpu_baseline": {"value": r["value"], "unit": "Msamples/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
                 "e2e": {"value": r["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line), flush=True)
+        emit(line)
         return
 
     import torch
@@ -161,6 +175,8 @@ def main():
     if world > 1:
         dmod.init_from_env()
     torch.cuda.set_device(local)
+    if a.workload == "c2":
+        return bench_c2(pkg, a, emit, local, torch)
     sc, name = make_scene(pkg, a.workload, a.spp)
     t0 = time.time()
     be = pkg.Backend(sc, local)
@@ -169,58 +185,82 @@ def main():
     W, H = sc.camera.resolution
     film = torch.zeros(H * W * 4, dtype=torch.float32, device="cuda")
     stream = torch.cuda.current_stream().cuda_stream
-    p = sc.integrator.params(rank=rank, world_size=world, shard_tile=32)
-    p.mode = pkg.abi.MODE_WAVEFRONT if a.mode == "wavefront" else pkg.abi.MODE_MEGAKERNEL
+    SPLITS = {"tile": pkg.abi.SPLIT_TILE, "sample": pkg.abi.SPLIT_SAMPLE}
+    split = "tile" if world == 1 else ("sample" if a.split == "auto" else a.split)
+
+    def params_for(split_name):
+        q = sc.integrator.params(rank=rank, world_size=world, shard_tile=32, split=SPLITS[split_name])
+        q.mode = pkg.abi.MODE_WAVEFRONT if a.mode == "wavefront" else pkg.abi.MODE_MEGAKERNEL
+        return q
+
+    p = params_for(split)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step():
-        st = be.render_device(film.data_ptr(), p, stream)
-        dmod.combine_film(film)
-        return st
+    def timed_steps(q, steps, warmup):
+        """`steps` frames: render this rank's share + the one film collective; device time, max over ranks."""
+        for _ in range(warmup):
+            be.render_device(film.data_ptr(), q, stream)
+            dmod.combine_film(film)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        acc = [0, 0, 0, 0]
+        for _ in range(steps):
+            st = be.render_device(film.data_ptr(), q, stream)
+            dmod.combine_film(film)
+            acc[0] += st.n_samples
+            acc[1] += st.n_closest_rays
+            acc[2] += st.n_shadow_rays
+            acc[3] += st.n_kernel_launches + 2  # + the two memsets of akb_render_device
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        tot = torch.tensor(acc, dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        return float(ms.item()), [float(x) for x in tot.tolist()]
 
-    for _ in range(a.warmup):
-        step()
     clocks = ClockSampler(local)
+    timed_steps(p, 0, a.warmup)
     if rank == 0:
         clocks.start()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    launches = samples = n_c = n_s = 0
-    for _ in range(a.steps):
-        st = step()
-        launches += st.n_kernel_launches + 2  # + the two memsets of akb_render_device
-        samples += st.n_samples
-        n_c += st.n_closest_rays
-        n_s += st.n_shadow_rays
-    e1.record()
-    barrier()
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
-    tot = torch.tensor([samples, n_c, n_s, launches], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms_total, (samples, n_c, n_s, launches) = timed_steps(p, a.steps, 0)
     clk = clocks.stop() if rank == 0 else None
-    ms_total = float(ms.item())
-    samples, n_c, n_s, launches = (float(x) for x in tot.tolist())
     value = samples / (ms_total * 1e-3) / 1e6
+    alt = None
+    if world > 1 and a.split == "auto":  # the bit-identical interleaved-tile split, timed the same way
+        ms_alt, tot_alt = timed_steps(params_for("tile"), a.steps, min(a.warmup, 3))
+        alt = {"split": "tile", "value": tot_alt[0] / (ms_alt * 1e-3) / 1e6, "unit": "Msamples/s",
+               "ms_per_step": ms_alt / a.steps,
+               "note": "interleaved 32x32 tiles: the combined film is bit-identical to the 1-GPU film"}
 
     # ---- end to end through the host-buffer C-ABI call a reference maintainer would bind (akb_render): every step
     # passes the parameters from host memory and reads the film back to a host buffer inside the timed region.
-    host_film = np.zeros((H, W, 4), np.float32)
+    # N > 1: each rank renders its share on the device, ONE reduce, rank 0 copies the combined film to pinned memory.
     e2e_steps = max(1, min(a.steps, 3))
-    be.render(p, out=host_film)
+    if world == 1:
+        host_film = np.zeros((H, W, 4), np.float32)
+        be.render(p, out=host_film)
+    else:
+        host_film = torch.empty(H * W * 4, dtype=torch.float32, pin_memory=True)
     barrier()
     t = time.perf_counter()
     e2e_samples = 0
     for _ in range(e2e_steps):
-        _, st = be.render(p, out=host_film)
+        if world == 1:
+            _, st = be.render(p, out=host_film)
+        else:
+            st = be.render_device(film.data_ptr(), p, stream)
+            dmod.combine_film(film)
+            if rank == 0:
+                host_film.copy_(film, non_blocking=False)
         e2e_samples += st.n_samples
-    torch.cuda.synchronize()
+    barrier()
     e2e_s = torch.tensor([time.perf_counter() - t], dtype=torch.float64, device="cuda")
     e2e_n = torch.tensor([float(e2e_samples)], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -273,23 +313,163 @@ def main():
         line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": a.steps,
                 "warmup": a.warmup, "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": name, "mode": a.mode, "parallelism": "tile%d" % world if world > 1 else "single",
-                           "tile": 32, "l2": "inputs larger than L2: BVH+triangles %.0f MB, shading records %.0f MB, path state %.0f MB"
+                "config": {"workload": name, "mode": a.mode,
+                           "parallelism": ("%s-split x%d, scene replicated, one NCCL sum-reduce of the film per frame" % (split, world))
+                           if world > 1 else "single", "tile": 32, "l2": "inputs larger than L2: BVH+triangles %.0f MB, shading records %.0f MB, path state %.0f MB"
                            % ((info["bvh_bytes"] + info["triangle_bytes"]) / 1e6, info["n_triangles"] * 96 / 1e6, W * H * 208 / 1e6),
                            "bvh_nodes": info["n_bvh_nodes"], "scene_build_s": round(build_s, 2)},
                 "clocks": clk,
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": C.sizeof(pkg.abi.RenderParams),
-                        "d2h_bytes_per_step": W * H * 16, "api": "akb_render (host film buffer)"},
+                        "d2h_bytes_per_step": W * H * 16,
+                        "api": "akb_render (host film buffer)" if world == 1 else "akb_render_device + film reduce + D2H on rank 0"},
                 "gpu_launches": int(launches),
                 "rays": {"closest_per_sample": n_c / samples, "shadow_per_sample": n_s / samples,
                          "mrays_per_s": (n_c + n_s) / (ms_total * 1e-3) / 1e6},
                 "roofline": roof, "cpu_baseline": cpu}
+        if alt:
+            line["alt_split"] = alt
         line.update(extras)
-        print(json.dumps(line), flush=True)
+        emit(line)
     be.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def bench_c2(pkg, a, emit, local, torch):
+    """C2 (BASELINE.json configs[1]): closest-hit / any-hit ray microbench against the 999 700-triangle
+    mesh M1: `--rays` (default 100 M) coherent rays = pinhole camera (0,20,70) pitch -15 deg, fov 60, 12500 x 8000 raster
+    in row-major order, and as many incoherent rays = cosine-hemisphere bounces off the primary hit points (misses:
+    uniform origins in the mesh box, uniform directions). tmin = 1e-3, tmax = inf; any-hit variant tmax = 50.
+    One step = the four launches (coherent/incoherent x closest/any). Rays are generated on the device with torch (bench
+    input, not product code). value = closest-hit rays per second over the coherent + incoherent sets."""
+    import math
+    n_rays = int(os.environ.get("AKB_C2_RAYS", "100000000"))
+    RW = 12500
+    RH = max(1, n_rays // RW)
+    n = RW * RH
+    sc = pkg.scenes.terrain_scene(n=708, resolution=(1920, 1080), spp=1, max_depth=1, materials="c3")
+    t0 = time.time()
+    be = pkg.Backend(sc, local)
+    build_s = time.time() - t0
+    info = be.info()
+    dev = "cuda"
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234)
+    cam = sc.camera
+    c2w = torch.tensor(cam.c2w(), device=dev)
+    s_ = math.atan(math.radians(cam.fov) / 2)
+    ix = torch.arange(n, device=dev, dtype=torch.int64)
+    px, py = (ix % RW).float() + 0.5, (ix // RW).float() + 0.5
+    x = (px / RW * 2 - 1) * s_
+    y = -(py / RH * 2 - 1) * s_ * RH / RW
+    dl = torch.stack([x, y, -torch.ones_like(x)], 1)
+    dl = dl / dl.norm(dim=1, keepdim=True)
+    d = dl @ c2w[:3, :3].T
+    org = torch.empty(n, 4, device=dev)
+    org[:, :3] = c2w[:3, 3]
+    org[:, 3] = 1e-3
+    dr = torch.empty(n, 4, device=dev)
+    dr[:, :3] = d
+    dr[:, 3] = float("inf")
+    del px, py, x, y, dl, d, ix
+    hits = torch.empty(n * 5, dtype=torch.int32, device=dev)
+    occ = torch.empty(n, dtype=torch.int32, device=dev)
+
+    def trace(o, dd, any_hit):
+        return be.trace_device(o.data_ptr(), dd.data_ptr(), n, any_hit, hits.data_ptr(), occ.data_ptr())
+
+    trace(org, dr, 0)
+    h = hits.view(n, 5)
+    prim = h[:, 3].long()
+    hit = prim >= 0
+    t = h[:, 0].contiguous().view(torch.float32)
+    mesh = sc.shapes[0]
+    V = torch.from_numpy(mesh.vertices.reshape(-1, 3)).to(dev)
+    I = torch.from_numpy(mesh.indices.reshape(-1, 3).astype(np.int64)).to(dev)
+    pc = prim.clamp(min=0)
+    v0, v1, v2 = V[I[pc, 0]], V[I[pc, 1]], V[I[pc, 2]]
+    ng = torch.linalg.cross(v1 - v0, v2 - v0)
+    ng = ng / ng.norm(dim=1, keepdim=True).clamp(min=1e-30)
+    del v0, v1, v2, pc
+    p = org[:, :3] + dr[:, :3] * torch.where(hit, t, torch.zeros_like(t))[:, None] + 1e-3 * ng
+    u = torch.rand(n, 2, device=dev, generator=g)
+    r, phi = u[:, 0].sqrt(), 2 * math.pi * u[:, 1]
+    lx, lz, ly = r * phi.cos(), r * phi.sin(), (1 - u[:, 0]).clamp(min=0).sqrt()
+    tang = torch.linalg.cross(ng, torch.tensor([1.0, 0.0, 0.0], device=dev).expand_as(ng))
+    tang = tang / tang.norm(dim=1, keepdim=True).clamp(min=1e-30)
+    bit = torch.linalg.cross(ng, tang)
+    d2 = lx[:, None] * tang + ly[:, None] * ng + lz[:, None] * bit
+    lo, hi = V.min(0).values, V.max(0).values
+    rnd_o = lo + (hi - lo) * torch.rand(n, 3, device=dev, generator=g)
+    rnd_d = torch.randn(n, 3, device=dev, generator=g)
+    rnd_d = rnd_d / rnd_d.norm(dim=1, keepdim=True)
+    org2 = torch.empty(n, 4, device=dev)
+    org2[:, :3] = torch.where(hit[:, None], p, rnd_o)
+    org2[:, 3] = 1e-3
+    dr2 = torch.empty(n, 4, device=dev)
+    dr2[:, :3] = torch.where(hit[:, None], d2, rnd_d)
+    dr2[:, 3] = float("inf")
+    del p, u, r, phi, lx, ly, lz, tang, bit, d2, rnd_o, rnd_d, ng, t, prim
+    dr_any, dr2_any = dr.clone(), dr2.clone()
+    dr_any[:, 3] = 50.0
+    dr2_any[:, 3] = 50.0
+    hit_frac = float(hit.float().mean().item())
+    sets = (("coherent_closest", org, dr, 0), ("incoherent_closest", org2, dr2, 0), ("coherent_any", org, dr_any, 1),
+            ("incoherent_any", org2, dr2_any, 1))
+    for _ in range(max(1, a.warmup)):
+        for _, o, dd, ah in sets:
+            trace(o, dd, ah)
+    clocks = ClockSampler(local)
+    clocks.start()
+    ms = {k: 0.0 for k, *_ in sets}
+    for _ in range(a.steps):
+        for k, o, dd, ah in sets:
+            ms[k] += trace(o, dd, ah)  # device time of the traversal launch (CUDA events on the launch stream)
+    clk = clocks.stop()
+    mrays = {k: n * a.steps / (v * 1e-3) / 1e6 for k, v in ms.items()}
+    closest_ms = ms["coherent_closest"] + ms["incoherent_closest"]
+    value = 2 * n * a.steps / (closest_ms * 1e-3) / 1e6
+    peak, peak_src = measured_peaks()
+    achieved = BYTES_CLOSEST * 2 * n * a.steps / (closest_ms * 1e-3) / 1e9
+    # ---- end to end: akb_trace with HOST ray and hit buffers (H2D + kernel + D2H inside the timed region), bounded set
+    m = min(n, 16 * 1024 * 1024)
+    ho, hd = org2[:m].cpu().numpy(), dr2[:m].cpu().numpy()
+    be.trace(ho[:1024], hd[:1024])
+    t0 = time.perf_counter()
+    be.trace(ho, hd)
+    e2e_s = time.perf_counter() - t0
+    # ---- CPU baseline: the reference's own BVH (Scene::intersect) over a bounded sample of the incoherent set
+    cpu = None
+    if not a.no_cpu_baseline:
+        try:
+            from oracle_libs import Oracle, Reference, have_ref
+            impl, kind = (Reference(sc), "reference") if have_ref() else (Oracle(sc), "port")
+            k = m
+            t0 = time.perf_counter()
+            impl.trace(ho[:k], hd[:k])
+            cpu_s = time.perf_counter() - t0
+            cpu = {"value": k / cpu_s / 1e6, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": kind,
+                   "sample": "first %d incoherent closest-hit rays of the same set, all host threads" % k}
+        except Exception as ex:
+            cpu = {"value": None, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: %r" % (ex,)}
+    line = {"metric": "closest-hit Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": 1, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": sum(ms.values()) / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "C2: %d coherent + %d incoherent rays vs the 999700-triangle mesh M1 (closest hit; any hit with tmax 50 beside it)" % (n, n),
+                       "l2": "inputs larger than L2: %.1f GB of rays + %.1f GB of hits per set" % (n * 32 / 1e9, n * 20 / 1e9),
+                       "bvh_nodes": info["n_bvh_nodes"], "scene_build_s": round(build_s, 2), "primary_hit_fraction": hit_frac},
+            "clocks": clk,
+            "e2e": {"value": m / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": m * 32, "d2h_bytes_per_step": m * 20,
+                    "api": "akb_trace (host ray + hit buffers), %d incoherent closest-hit rays" % m},
+            "gpu_launches": 4 * a.steps, "mrays_per_s": mrays,
+            "roofline": {"bound": "hbm", "kernel": "trace_batch_kernel (closest hit)", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "bytes_per_launch": BYTES_CLOSEST * n, "avg_launch_ms": closest_ms / (2 * a.steps),
+                         "note": "52 B per closest-hit ray (32 B ray + 20 B hit); traversal is issue/latency-bound, see profiles/"},
+            "cpu_baseline": cpu}
+    emit(line)
+    be.close()
 
 
 def ray_microbench(pkg, be, torch):

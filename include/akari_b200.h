@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define AKB_ABI_VERSION 1
+#define AKB_ABI_VERSION 2
 
 typedef enum akb_status {
     AKB_OK = 0,
@@ -99,6 +99,17 @@ typedef struct akb_scene_desc {
 typedef enum akb_integrator { AKB_INTEGRATOR_PATH = 0, AKB_INTEGRATOR_AO = 1 } akb_integrator;
 typedef enum akb_sampler { AKB_SAMPLER_LCG = 0, AKB_SAMPLER_PCG = 1 } akb_sampler; /* kernel/sampler.h:28-66 */
 typedef enum akb_mode { AKB_MODE_WAVEFRONT = 0, AKB_MODE_MEGAKERNEL = 1 } akb_mode; /* Path{wavefront|megakernel} */
+/* How `world_size` processes (one per GPU) share a frame. The reference shards tiles over CPU threads
+ * (kernel/integrators/cpu/integrator.cpp:115-141) and has no multi-GPU path. */
+typedef enum akb_split {
+    AKB_SPLIT_TILE = 0,  /* interleaved tile_size^2 tiles, owner = tile_id % world_size; pixels this rank does not own
+                            stay zero; the sum over ranks is bit-identical to the single-process film */
+    AKB_SPLIT_SAMPLE = 1 /* every rank renders every pixel with spp/world_size samples (the first spp % world_size
+                            ranks take one more) from per-rank sampler seeds x + y*W + rank*W*H; the sum over ranks
+                            is a `spp`-sample estimate of the same image, not bit-identical to the single-process
+                            one (the reference's per-pixel sampler stream is sequential and cannot be skipped ahead).
+                            Rank 0's share is bit-identical to a single-process render at that sample count. */
+} akb_split;
 
 typedef struct akb_render_params {
     int32_t integrator;     /* akb_integrator */
@@ -116,6 +127,7 @@ typedef struct akb_render_params {
     int32_t rank;
     int32_t world_size;
     int32_t tile_size;
+    int32_t split;          /* akb_split */
 } akb_render_params;
 
 /* Per-render statistics (the reference prints per-kernel cudaEvent stats, kernel/cuda/launch.cpp:92-118). */

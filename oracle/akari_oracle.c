@@ -732,9 +732,14 @@ static void *render_worker(void *arg) {
         if (y >= j->y1) break;
         for (int x = j->x0; x < j->x1; x++) {
             sampler_t smp; memset(&smp, 0, sizeof smp); smp.kind = p->sampler;
-            sampler_set_index(&smp, (uint64_t)(x + (int)y * W));
+            /* AKB_SPLIT_SAMPLE (include/akari_b200.h): this rank's share of the samples, per-rank seed offset */
+            const int world = p->world_size > 0 ? p->world_size : 1;
+            const int sample_split = p->split == AKB_SPLIT_SAMPLE;
+            const int spp = sample_split ? p->spp / world + (p->rank < p->spp % world ? 1 : 0) : p->spp;
+            const uint64_t seed_off = sample_split ? (uint64_t)p->rank * (uint64_t)W * (uint64_t)j->s->cam.h : 0;
+            sampler_set_index(&smp, (uint64_t)(x + (int)y * W) + seed_off);
             v3 sum = {0, 0, 0}; float weight = 0;
-            for (int sidx = 0; sidx < p->spp; sidx++) {
+            for (int sidx = 0; sidx < spp; sidx++) {
                 if (p->integrator == AKB_INTEGRATOR_AO) { /* cpu/integrator.cpp:72-80 */
                     float g = run_ao(j->s, &smp, x, (int)y, p->ao_occlude, &c1);
                     weight += 1.0f; sum = add3(sum, mk3(g, g, g));

@@ -38,17 +38,18 @@ template <class F> void parallel_rows(int n, int threads, F f) {
 template <int SAMP> void render_rows(HC *h, const akb_render_params *p, float *out, int threads) {
     const SceneDev &S = h->dev;
     const int W = S.cam.width, H = S.cam.height;
-    SlotMap sm = make_slot_map(W, H, p->tile_size > 0 ? p->tile_size : 32, p->rank, p->world_size > 0 ? p->world_size : 1);
+    const Shard shard = make_shard(W, H, p);
+    const SlotMap sm = shard.map;
     const int tt = sm.tile * sm.tile;
     parallel_rows(sm.n_owned_tiles, threads, [&](int lt) {
         for (int in = 0; in < tt; in++) {
             int x, y;
             if (!slot_to_pixel(sm, lt * tt + in, x, y)) continue;
             Rng<SAMP> rng;
-            rng.set_sample_index((uint64_t)(x + y * W));
+            rng.set_sample_index((uint64_t)(x + y * W) + shard.seed_offset);
             v3 sum = mk3(0, 0, 0);
             float weight = 0;
-            for (int s = 0; s < p->spp; s++) {
+            for (int s = 0; s < shard.spp; s++) {
                 if (p->integrator == AKB_INTEGRATOR_AO) { // the body of ao_kernel (csrc/kernels.cu)
                     float u1x, u1y, u2x, u2y;
                     rng.next2d(u2x, u2y);

@@ -147,6 +147,28 @@ def test_tile_sharding_is_exact():
     be.close()
 
 
+def test_sample_split_matches_oracle_and_converges():
+    """AKB_SPLIT_SAMPLE: every rank's film is bit-identical to the oracle's for that rank (same seeds), and the combined
+    estimate is statistically the same image as the single-GPU one (both compared with a high-spp render)."""
+    sc = scenes.mixed_box((64, 48), 10, 4)
+    be = backend(sc)
+    o = Oracle(sc)
+    total = None
+    for r in range(4):
+        p = sc.integrator.params(rank=r, world_size=4, split=abi.SPLIT_SAMPLE)
+        film, st = be.render(p)
+        assert (film[..., 3] == (3.0 if r < 2 else 2.0)).all()
+        assert n_diff_px(film, o.render(p)) <= 2
+        total = film if total is None else total + film
+    assert (total[..., 3] == 10.0).all()
+    single, _ = be.render(sc.integrator.params())
+    sc_hi = scenes.mixed_box((64, 48), 2048, 4)
+    hi, _ = backend(sc_hi).render(sc_hi.integrator.params())
+    e_split, e_single = rel_rmse(total, hi), rel_rmse(single, hi)
+    assert 0.6 < e_split / e_single < 1.6, (e_split, e_single)
+    be.close()
+
+
 def test_edge_cases():
     lib = pkg.init(0)
     # empty scene, spp 0, depth 0, no lights
