@@ -444,7 +444,8 @@ def bench_c2(pkg, a, emit, local, torch):
     if not a.no_cpu_baseline:
         try:
             from oracle_libs import Oracle, Reference, have_ref
-            impl, kind = (Reference(sc), "reference") if have_ref() else (Oracle(sc), "port")
+            sc_ref = pkg.scenes.terrain_scene(n=708, resolution=(1920, 1080), spp=1, max_depth=1, materials="c3ref")  # same mesh
+            impl, kind = (Reference(sc_ref), "reference") if have_ref() else (Oracle(sc_ref), "port")
             k = m
             t0 = time.perf_counter()
             impl.trace(ho[:k], hd[:k])
