@@ -21,6 +21,8 @@ int g_device = -1;
 int g_n_sms = 0;
 constexpr size_t kMaxBatch = (size_t)1 << 30;
 bool g_profile_stages = false;
+int g_pipelines = 2;                   // AKB_PIPELINES: half-frame pipelines of the wavefront (1 or 2)
+int g_pipeline_min_slots = 128 * 1024; // AKB_PIPELINE_MIN_SLOTS: below this one pipeline keeps the launches large
 
 akb_status set_err(akb_status st, const char *fmt, ...) {
     char buf[512];
@@ -58,7 +60,9 @@ struct akb_scene {
     Workspace ws;
     std::vector<void *> ws_allocs;
     int ws_slots = 0;
-    Counters *d_ctr = nullptr, *h_ctr = nullptr;
+    Counters *d_ctr = nullptr, *h_ctr = nullptr; // [2]: one per half-frame pipeline
+    cudaStream_t aux_stream = nullptr;           // second pipeline's stream
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     float4 *d_film = nullptr;
     size_t d_film_px = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -74,6 +78,9 @@ struct akb_scene {
         if (d_ctr) cudaFree(d_ctr);
         if (h_ctr) cudaFreeHost(h_ctr);
         if (d_film) cudaFree(d_film);
+        if (aux_stream) cudaStreamDestroy(aux_stream);
+        if (ev_fork) cudaEventDestroy(ev_fork);
+        if (ev_join) cudaEventDestroy(ev_join);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
     }
@@ -118,9 +125,23 @@ akb_status ensure_workspace(akb_scene *sc, int n_slots) {
     }
 #undef WS
     w.ctr = sc->d_ctr;
+    w.slot_base = 0;
     w.n_slots = n_slots;
     sc->ws_slots = n_slots;
     return AKB_OK;
+}
+
+// The slots [base, base + n) of the frame's workspace as a workspace of their own (own queues, own counters).
+Workspace workspace_view(const Workspace &w, int base, int n, Counters *ctr) {
+    Workspace v = w;
+    v.n_slots = n, v.slot_base = w.slot_base + base, v.ctr = ctr;
+    v.ray_o += base, v.ray_d += base, v.hit += base, v.beta += base, v.L += base, v.rng += base;
+    v.sh_o += base, v.sh_d += base, v.sh_c += base, v.acc += base;
+    for (int b = 0; b < 2; b++) {
+        v.q_ext[b] += base, v.q_sh[b] += base;
+        for (int k = 0; k < kNumKeys; k++) v.q_shade[b][k] += base;
+    }
+    return v;
 }
 
 akb_status check_ready(const char *who) {
@@ -163,6 +184,8 @@ akb_status akb_init(int device_index) {
     if (h_res != 1) return set_err(AKB_CUDA_ERROR, "akb_init: kernels were built with FMA contraction; rebuild with -fmad=false");
     const char *pf = getenv("AKB_PROFILE_STAGES");
     g_profile_stages = pf && pf[0] == '1';
+    if (const char *e = getenv("AKB_PIPELINES")) g_pipelines = atoi(e);
+    if (const char *e = getenv("AKB_PIPELINE_MIN_SLOTS")) g_pipeline_min_slots = atoi(e);
     if (const char *rb = getenv("AKB_REFILL_BELOW")) {
         int v = atoi(rb);
         if (v >= 1 && v <= 32) CU(set_refill_below(v));
@@ -193,16 +216,28 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
     akb_scene *sc = new akb_scene();
     SceneDev &S = sc->dev;
     memset(&S, 0, sizeof S);
-    st = upload(sc, (const float4 *)hs.bvh.nodes.data(), hs.bvh.nodes.size() * 5, &S.nodes);
-    if (st == AKB_OK) st = upload(sc, (const float4 *)hs.tris.data(), hs.tris.size(), &S.tris);
+    { // BVH nodes and leaf triangles share one allocation (the traversal working set: 56 MB for 1 M triangles)
+        const size_t node_f4 = hs.bvh.nodes.size() * 5, node_pad = (node_f4 + 15) & ~(size_t)15, tri_f4 = hs.tris.size();
+        float4 *buf = nullptr;
+        const size_t bytes = std::max<size_t>((node_pad + tri_f4) * sizeof(float4), 16);
+        cudaError_t e = cudaMalloc((void **)&buf, bytes);
+        if (e == cudaSuccess) sc->allocs.push_back(buf);
+        if (e == cudaSuccess && node_f4) e = cudaMemcpy(buf, hs.bvh.nodes.data(), node_f4 * sizeof(float4), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess && tri_f4) e = cudaMemcpy(buf + node_pad, hs.tris.data(), tri_f4 * sizeof(float4), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) st = set_err(e == cudaErrorMemoryAllocation ? AKB_OOM : AKB_CUDA_ERROR, "akb_scene_create: %s", cudaGetErrorString(e));
+        S.nodes = buf, S.tris = buf + node_pad;
+    }
     if (st == AKB_OK) st = upload(sc, (const float4 *)hs.shading.data(), hs.shading.size(), &S.shading);
     if (st == AKB_OK) st = upload(sc, hs.mats.data(), hs.mats.size(), &S.mats);
     if (st == AKB_OK) st = upload(sc, (const float4 *)hs.lights.data(), hs.lights.size(), &S.lights);
     if (st == AKB_OK) st = upload(sc, hs.light_cdf.data(), hs.light_cdf.size(), &S.light_cdf);
     if (st == AKB_OK) st = upload(sc, hs.light_func.data(), hs.light_func.size(), &S.light_func);
     if (st == AKB_OK) {
-        cudaError_t e = cudaMalloc((void **)&sc->d_ctr, sizeof(Counters));
-        if (e == cudaSuccess) e = cudaMallocHost((void **)&sc->h_ctr, sizeof(Counters));
+        cudaError_t e = cudaMalloc((void **)&sc->d_ctr, 2 * sizeof(Counters));
+        if (e == cudaSuccess) e = cudaMallocHost((void **)&sc->h_ctr, 2 * sizeof(Counters));
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&sc->aux_stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_fork, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_join, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreate(&sc->ev0);
         if (e == cudaSuccess) e = cudaEventCreate(&sc->ev1);
         if (e != cudaSuccess) st = set_err(AKB_CUDA_ERROR, "akb_scene_create: %s", cudaGetErrorString(e));
@@ -269,7 +304,7 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
     uint64_t launches = 0;
     std::vector<cudaEvent_t> evs;
     CU(cudaMemsetAsync(d_out_rgbw, 0, n_px * sizeof(float4), stream));
-    CU(cudaMemsetAsync(sc->d_ctr, 0, sizeof(Counters), stream));
+    CU(cudaMemsetAsync(sc->d_ctr, 0, 2 * sizeof(Counters), stream));
     CU(cudaEventRecord(sc->ev0, stream));
     if (p->integrator == AKB_INTEGRATOR_AO) {
         CU(launch_ao(sc->dev, rc, p->ao_occlude, (float4 *)d_out_rgbw, sc->d_ctr, stream));
@@ -278,10 +313,30 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
         CU(launch_megakernel(sc->dev, rc, (float4 *)d_out_rgbw, sc->d_ctr, stream));
         launches = 1;
     } else {
-        st = ensure_workspace(sc, rc.map.n_slots());
+        const int n_total = rc.map.n_slots();
+        st = ensure_workspace(sc, n_total);
         if (st != AKB_OK) return st;
-        CU(launch_wf_init(sc->dev, rc, sc->ws, g_n_sms, stream));
-        launches++;
+        // Two half-frame pipelines on two streams: while one half's traversal launch drains (persistent warps running
+        // their last, longest rays at a few lanes each) the other half's kernels fill the machine. Halves are whole
+        // tiles, so every slot keeps its pixel, seed and accumulation order: the film is unchanged.
+        const int tt = rc.map.tile * rc.map.tile;
+        const int n_pipes = (g_pipelines >= 2 && !g_profile_stages && rc.map.n_owned_tiles >= 2 && n_total >= g_pipeline_min_slots) ? 2 : 1;
+        const int base1 = n_pipes == 2 ? (rc.map.n_owned_tiles / 2) * tt : n_total;
+        struct Pipe {
+            Workspace ws;
+            cudaStream_t st;
+            bool live;
+        } pipe[2];
+        pipe[0] = Pipe{workspace_view(sc->ws, 0, base1, sc->d_ctr), stream, n_total > 0 && rc.spp > 0};
+        pipe[1] = Pipe{workspace_view(sc->ws, base1, n_total - base1, sc->d_ctr + 1), sc->aux_stream, n_pipes == 2 && rc.spp > 0};
+        if (n_pipes == 2) {
+            CU(cudaEventRecord(sc->ev_fork, stream));
+            CU(cudaStreamWaitEvent(sc->aux_stream, sc->ev_fork, 0));
+        }
+        for (int q = 0; q < n_pipes; q++) {
+            CU(launch_wf_init(sc->dev, rc, pipe[q].ws, g_n_sms, pipe[q].st));
+            launches++;
+        }
         const long max_it = (long)rc.spp * (rc.max_depth + 2) + 2;
         const int check_every = 4;
         auto mark = [&]() {
@@ -293,30 +348,49 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
             return cudaEventRecord(e, stream);
         };
         CU(mark());
-        for (long it = 0; it < max_it && rc.map.n_slots() > 0 && rc.spp > 0; it++) {
+        for (long it = 0; it < max_it && (pipe[0].live || pipe[1].live); it++) {
             const int b = (int)(it & 1);
-            CU(launch_wf_trace(sc->dev, rc, sc->ws, b, g_n_sms, stream));
+            for (int q = 0; q < n_pipes; q++)
+                if (pipe[q].live) {
+                    CU(launch_wf_trace(sc->dev, rc, pipe[q].ws, b, g_n_sms, pipe[q].st));
+                    launches++;
+                }
             CU(mark());
-            CU(launch_wf_shade(sc->dev, rc, sc->ws, b, g_n_sms, stream));
+            for (int q = 0; q < n_pipes; q++)
+                if (pipe[q].live) {
+                    CU(launch_wf_shade(sc->dev, rc, pipe[q].ws, b, g_n_sms, pipe[q].st));
+                    launches++;
+                }
             CU(mark());
-            launches += 2;
             if ((it % check_every) == check_every - 1) {
-                CU(cudaMemcpyAsync(sc->h_ctr, sc->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
-                CU(cudaStreamSynchronize(stream));
-                if (sc->h_ctr->n_ext[b ^ 1] == 0 && sc->h_ctr->n_sh[b ^ 1] == 0) break;
+                for (int q = 0; q < n_pipes; q++)
+                    if (pipe[q].live) CU(cudaMemcpyAsync(sc->h_ctr + q, sc->d_ctr + q, sizeof(Counters), cudaMemcpyDeviceToHost, pipe[q].st));
+                for (int q = 0; q < n_pipes; q++)
+                    if (pipe[q].live) {
+                        CU(cudaStreamSynchronize(pipe[q].st));
+                        if (sc->h_ctr[q].n_ext[b ^ 1] == 0 && sc->h_ctr[q].n_sh[b ^ 1] == 0) pipe[q].live = false;
+                    }
             }
         }
-        CU(launch_wf_resolve(rc, sc->ws, (float4 *)d_out_rgbw, stream));
-        launches++;
+        if (n_pipes == 2) {
+            CU(cudaEventRecord(sc->ev_join, sc->aux_stream));
+            CU(cudaStreamWaitEvent(stream, sc->ev_join, 0));
+        }
+        for (int q = 0; q < n_pipes; q++) {
+            CU(launch_wf_resolve(rc, pipe[q].ws, (float4 *)d_out_rgbw, stream));
+            launches++;
+        }
     }
     CU(cudaEventRecord(sc->ev1, stream));
-    CU(cudaMemcpyAsync(sc->h_ctr, sc->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+    CU(cudaMemcpyAsync(sc->h_ctr, sc->d_ctr, 2 * sizeof(Counters), cudaMemcpyDeviceToHost, stream));
     CU(cudaStreamSynchronize(stream));
     if (stats) {
         memset(stats, 0, sizeof *stats);
-        stats->n_samples = sc->h_ctr->stat_samples;
-        stats->n_closest_rays = sc->h_ctr->stat_closest - sc->h_ctr->stat_skipped;
-        stats->n_shadow_rays = sc->h_ctr->stat_shadow;
+        for (int q = 0; q < 2; q++) {
+            stats->n_samples += sc->h_ctr[q].stat_samples;
+            stats->n_closest_rays += sc->h_ctr[q].stat_closest - sc->h_ctr[q].stat_skipped;
+            stats->n_shadow_rays += sc->h_ctr[q].stat_shadow;
+        }
         stats->n_kernel_launches = launches;
         CU(cudaEventElapsedTime(&stats->ms_total, sc->ev0, sc->ev1));
         if (evs.size() >= 3) {

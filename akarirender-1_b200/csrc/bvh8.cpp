@@ -4,6 +4,8 @@
 // reference; the algorithm is different on purpose (no spatial splits, one level, wide nodes).
 #include "bvh8.h"
 
+#include <stdlib.h>
+
 #include <math.h>
 #include <string.h>
 
@@ -29,7 +31,12 @@ inline float half_area(const float *lo, const float *hi) {
 
 constexpr int kBins = 16;
 constexpr int kMaxLeaf = 3;       // a CWBVH leaf slot addresses at most 3 triangles (unary-coded count)
-constexpr float kTraversalCost = 0.5f;
+// Cost-model constants, overridable for tuning runs (AKB_BVH_TRAV_COST / AKB_BVH_PRIM_COST); see profiles/ for the sweep.
+static float env_float(const char *name, float dflt) {
+    const char *e = getenv(name);
+    return e && *e ? (float)atof(e) : dflt;
+}
+static const float kTraversalCost = env_float("AKB_BVH_TRAV_COST", 0.5f);
 
 struct Builder {
     const float *lo, *hi; // padded triangle boxes
@@ -265,7 +272,7 @@ struct Collapser {
     //   C_distribute(n,j) = min_{0<k<j} C(left,k) + C(right,j-k)
     // cost[n][i-1] = C(n,i); split[n][i-1] = k of the best distribution for i roots (0: use C(n,i-1));
     // kind[n]: the single-root choice (leaf or wide node); split8[n]: k of C_distribute(n,8).
-    static constexpr float kNodeCost = 1.0f, kPrimCost = 0.3f;
+    const float kNodeCost = 1.0f, kPrimCost = env_float("AKB_BVH_PRIM_COST", 0.3f);
     std::vector<float> cost;
     std::vector<uint8_t> split, split8, kind;
 

@@ -309,7 +309,7 @@ template <int SAMP> __global__ void __launch_bounds__(256) wf_init_kernel(SceneD
     const int n_pad = (n + 31) & ~31;
     for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_pad; slot += gridDim.x * blockDim.x) {
         int x = 0, y = 0;
-        const bool valid = slot < n && slot_to_pixel(rc.map, slot, x, y) && rc.spp > 0;
+        const bool valid = slot < n && slot_to_pixel(rc.map, slot + ws.slot_base, x, y) && rc.spp > 0;
         if (slot < n) ws.acc[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (valid) {
             Rng<SAMP> rng;
@@ -480,7 +480,7 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
                 n_done++;
                 if (done < rc.spp) {
                     int x, y;
-                    slot_to_pixel(rc.map, (int)slot, x, y);
+                    slot_to_pixel(rc.map, (int)slot + ws.slot_base, x, y);
                     start_sample<SAMP>(S, ws, (int)slot, x, y, ps.rng, done);
                     push_ext = true;
                 }
@@ -505,7 +505,7 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
 __global__ void wf_resolve_kernel(RenderConfig rc, Workspace ws, float4 *__restrict__ film) {
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     int x, y;
-    if (slot < ws.n_slots && slot_to_pixel(rc.map, slot, x, y)) film[(size_t)y * rc.map.width + x] = ws.acc[slot];
+    if (slot < ws.n_slots && slot_to_pixel(rc.map, slot + ws.slot_base, x, y)) film[(size_t)y * rc.map.width + x] = ws.acc[slot];
 }
 
 template <class K> int blocks_per_sm(K kernel, int block) {

@@ -22,6 +22,7 @@ struct Counters {
 // SOA<PathState>, RayQueue, ShadowRayQueue, MaterialQueue: kernel/integrators/gpu/workitem.h:27-107).
 struct Workspace {
     int n_slots;
+    int slot_base;              // this view's first slot in the frame's slot map (two half-frame pipelines, api.cu)
     float4 *ray_o, *ray_d;      // extension ray: (o|tmin) (d|tmax)
     float4 *hit;                // (u, v, tri id bits, material bits), tri < 0 = miss
     float4 *beta;               // (beta | depth bits)

@@ -165,7 +165,8 @@ int akb_device_count(void);
 akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene);
 akb_status akb_scene_destroy(akb_scene *scene);
 
-/* Scene facts (for tests/benches): 0 n_triangles, 1 n_bvh_nodes, 2 bvh_bytes, 3 n_lights, 4 triangle_bytes. */
+/* Scene facts (for tests/benches): 0 n_triangles, 1 n_bvh_nodes, 2 bvh_bytes, 3 n_lights, 4 triangle_bytes,
+ * 5 bvh_depth, 6 build_us. */
 uint64_t akb_scene_info(const akb_scene *scene, int what);
 
 /* ---- the hot path ------------------------------------------------------------------------------------ */
