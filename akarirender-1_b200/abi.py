@@ -6,7 +6,7 @@ built: there is no CPU fallback on the product path.
 import ctypes as C
 import os
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 OK, INVALID_ARG, CUDA_ERROR, NCCL_ERROR, OOM, NO_DEVICE = range(6)
 MAT_DIFFUSE, MAT_GLOSSY, MAT_EMISSIVE, MAT_MIX, MAT_DIELECTRIC = range(5)
@@ -18,7 +18,12 @@ SPLIT_TILE, SPLIT_SAMPLE = 0, 1
 
 class Material(C.Structure):
     _fields_ = [("type", C.c_int32), ("color", C.c_float * 3), ("roughness", C.c_float), ("fraction", C.c_float),
-                ("child_a", C.c_int32), ("child_b", C.c_int32), ("double_sided", C.c_int32), ("ior", C.c_float)]
+                ("child_a", C.c_int32), ("child_b", C.c_int32), ("double_sided", C.c_int32), ("ior", C.c_float),
+                ("color_tex", C.c_int32), ("roughness_tex", C.c_int32), ("fraction_tex", C.c_int32)]
+
+
+class Texture(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("rgba", C.POINTER(C.c_float))]
 
 
 class Mesh(C.Structure):
@@ -37,7 +42,7 @@ class Camera(C.Structure):
 class SceneDesc(C.Structure):
     _fields_ = [("abi_version", C.c_uint32), ("n_meshes", C.c_uint32), ("meshes", C.POINTER(Mesh)),
                 ("n_materials", C.c_uint32), ("_pad", C.c_uint32), ("materials", C.POINTER(Material)),
-                ("camera", Camera)]
+                ("camera", Camera), ("n_textures", C.c_uint32), ("_pad2", C.c_uint32), ("textures", C.POINTER(Texture))]
 
 
 class RenderParams(C.Structure):

@@ -232,6 +232,12 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
     if (st == AKB_OK) st = upload(sc, (const float4 *)hs.lights.data(), hs.lights.size(), &S.lights);
     if (st == AKB_OK) st = upload(sc, hs.light_cdf.data(), hs.light_cdf.size(), &S.light_cdf);
     if (st == AKB_OK) st = upload(sc, hs.light_func.data(), hs.light_func.size(), &S.light_func);
+    if (st == AKB_OK && !hs.tex_info.empty()) { // image textures: texels, per-texture info, per-triangle / per-light texcoords
+        st = upload(sc, (const float4 *)hs.texels.data(), hs.texels.size(), &S.texels);
+        if (st == AKB_OK) st = upload(sc, (const int4 *)hs.tex_info.data(), hs.tex_info.size() / 4, &S.tex_info);
+        if (st == AKB_OK) st = upload(sc, (const float4 *)hs.tri_tc.data(), hs.tri_tc.size(), &S.tri_tc);
+        if (st == AKB_OK) st = upload(sc, (const float4 *)hs.light_tc.data(), hs.light_tc.size(), &S.light_tc);
+    }
     if (st == AKB_OK) {
         cudaError_t e = cudaMalloc((void **)&sc->d_ctr, 2 * sizeof(Counters));
         if (e == cudaSuccess) e = cudaMallocHost((void **)&sc->h_ctr, 2 * sizeof(Counters));
@@ -249,6 +255,7 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
     S.light_func_int = hs.light_func_int;
     S.n_lights = (int)hs.light_func.size();
     S.n_mats = (int)hs.mats.size();
+    S.n_textures = (int)(hs.tex_info.size() / 4);
     S.cam = hs.cam;
     sc->n_tris = hs.n_tris, sc->n_nodes = hs.bvh.nodes.size(), sc->bvh_bytes = hs.bvh.nodes.size() * sizeof(Node8);
     sc->n_lights = hs.light_func.size(), sc->tri_bytes = hs.tris.size() * sizeof(f4);

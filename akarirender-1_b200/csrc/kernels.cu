@@ -362,7 +362,11 @@ template <int SAMP> struct WfSrc {
                             peek.s = ws.rng[slot];
                             float ux, uy, cp;
                             peek.next2d(ux, uy);
-                            type = S.mats[select_material(S.mats, T.hit.mat, ux, cp)].type;
+                            float tu = 0.f, tv = 0.f;
+                            if (S.n_textures)
+                                tri_texcoord(__ldg(S.tri_tc + 2 * (size_t)T.hit.tri), __ldg(S.tri_tc + 2 * (size_t)T.hit.tri + 1),
+                                             T.hit.u, T.hit.v, tu, tv);
+                            type = S.mats[select_material(S, T.hit.mat, ux, tu, tv, cp)].type;
                         }
                         key = type == AKB_MAT_DIFFUSE ? 1 : (type == AKB_MAT_GLOSSY ? 2 : (type == AKB_MAT_DIELECTRIC ? 3 : 0));
                     }

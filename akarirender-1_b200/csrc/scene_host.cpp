@@ -85,7 +85,27 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
                                       (uint32_t)m.child_b >= d->n_materials))
             return fail("akb_scene_create: Mix child out of range");
     }
-    if (hs->mats.empty()) hs->mats.push_back(akb_material{AKB_MAT_DIFFUSE, {0, 0, 0}, 0, 0, -1, -1, 0, 0});
+    if (d->n_textures && !d->textures) return fail("akb_scene_create: textures == NULL");
+    for (uint32_t i = 0; i < d->n_materials; i++) {
+        const akb_material &m = hs->mats[i];
+        for (int32_t t : {m.color_tex, m.roughness_tex, m.fraction_tex})
+            if (t < -1 || (t >= 0 && (uint32_t)t >= d->n_textures)) return fail("akb_scene_create: texture index out of range");
+    }
+    std::vector<float> tex_integral(d->n_textures, 0.f);
+    for (uint32_t i = 0; i < d->n_textures; i++) {
+        const akb_texture &t = d->textures[i];
+        if (t.width <= 0 || t.height <= 0 || !t.rgba) return fail("akb_scene_create: bad texture");
+        const size_t n = (size_t)t.width * t.height, first = hs->texels.size();
+        if (first + n >= (1ull << 31)) return fail("akb_scene_create: more than 2^31 texels");
+        hs->tex_info.insert(hs->tex_info.end(), {(int32_t)first, t.width, t.height, 0});
+        hs->texels.resize(first + n);
+        memcpy(&hs->texels[first], t.rgba, n * sizeof(f4));
+        float I = 0; // ImageTexture::integral, kernel/texture.h:50-56: sequential float sum of luminances / (w*h)
+        for (size_t k = 0; k < n; k++)
+            I += dot3(mk3(t.rgba[4 * k], t.rgba[4 * k + 1], t.rgba[4 * k + 2]), mk3((float)0.2126, (float)0.7152, (float)0.0722));
+        tex_integral[i] = I / (float)(t.width * t.height);
+    }
+    if (hs->mats.empty()) hs->mats.push_back(akb_material{AKB_MAT_DIFFUSE, {0, 0, 0}, 0, 0, -1, -1, 0, 0, -1, -1, -1});
     hs->geom_offset.resize(d->n_meshes + 1);
     uint64_t nt = 0;
     for (uint32_t g = 0; g < d->n_meshes; g++) {
@@ -99,6 +119,8 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
     if (nt >= (1ull << 31)) return fail("akb_scene_create: more than 2^31 triangles");
     hs->n_tris = nt;
     hs->shading.resize(6 * nt);
+    const bool textured = d->n_textures > 0;
+    if (textured) hs->tri_tc.resize(2 * nt);
     std::vector<float> blo(3 * nt), bhi(3 * nt);
     std::vector<f4> leaf_rec(3 * nt); // flat order first; permuted after the build
     float max_abs = 0;
@@ -135,6 +157,11 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
                 blo[3 * t + a] = lo, bhi[3 * t + a] = hi;
                 if (isfinite(lo) && isfinite(hi)) max_abs = fmaxf(max_abs, fmaxf(fabsf(lo), fabsf(hi)));
             }
+            if (textured) {
+                const float *tc = m.texcoords ? m.texcoords + 6 * p : nullptr;
+                hs->tri_tc[2 * t] = tc ? f4{tc[0], tc[1], tc[2], tc[3]} : f4{0, 0, 0, 0};
+                hs->tri_tc[2 * t + 1] = tc ? f4{tc[4], tc[5], 0, 0} : f4{0, 0, 0, 0};
+            }
             if (mat >= 0 && hs->mats[mat].type == AKB_MAT_EMISSIVE) {
                 LightSrc ls;
                 ls.tri = t;
@@ -149,6 +176,7 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
     // area lights in (mesh, prim) order + power distribution, core/nodes/scene.cpp:58-92
     const size_t nl = light_src.size();
     hs->lights.resize(4 * nl);
+    if (textured) hs->light_tc.resize(2 * nl);
     hs->light_func.resize(nl);
     hs->light_cdf.assign(nl + 1, 0.f);
     for (size_t k = 0; k < nl; k++) {
@@ -168,7 +196,13 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
         hs->lights[4 * k + 3] = mkf4(lng, color.z);
         // power = |e1 x e2| * texcoord area * integral(texture) (core/nodes/scene.cpp:76-88);
         // ConstantTexture::integral = luminance (kernel/texture.h:36, common/color.h:52-56)
-        const float I = dot3(color, mk3((float)0.2126, (float)0.7152, (float)0.0722));
+        const int32_t ctex = hs->mats[mat].color_tex;
+        const float I = ctex >= 0 ? tex_integral[ctex] : dot3(color, mk3((float)0.2126, (float)0.7152, (float)0.0722));
+        if (textured) {
+            const float(*uv)[2] = light_src[k].uv;
+            hs->light_tc[2 * k] = f4{uv[0][0], uv[0][1], uv[1][0], uv[1][1]};
+            hs->light_tc[2 * k + 1] = f4{uv[2][0], uv[2][1], i2f(ctex), 0};
+        }
         v3 tc[3];
         for (int j = 0; j < 3; j++) tc[j] = mk3(light_src[k].uv[j][0], light_src[k].uv[j][1], 0.0f);
         const v3 tcc = cross3(sub3(tc[1], tc[0]), sub3(tc[2], tc[0]));

@@ -25,6 +25,12 @@ struct HostScene {
     std::vector<f4> shading; // 6 per triangle, flat order
     std::vector<akb_material> mats;
     std::vector<f4> lights; // 4 per light
+    // image textures (only filled when the description has any): texels of all textures back to back, per texture
+    // (first texel, width, height, 0), per triangle (flat order) and per light the three corner texcoords
+    std::vector<f4> texels;
+    std::vector<int32_t> tex_info; // 4 per texture
+    std::vector<f4> tri_tc;        // 2 per triangle: (u0,v0,u1,v1) (u2,v2,-,-)
+    std::vector<f4> light_tc;      // 2 per light:    (u0,v0,u1,v1) (u2,v2,texture id bits,-)
     std::vector<float> light_func, light_cdf;
     float light_func_int = 0;
     CameraDev cam;

@@ -89,6 +89,12 @@ struct SceneDev {
     float light_func_int;
     int n_lights;
     int n_mats;
+    // image textures (kernel/texture.h:39-57); n_textures == 0 for every BASELINE config, and then none of this is read
+    int n_textures;
+    const float4 *texels;   // all textures back to back, RGBA
+    const int4 *tex_info;   // (first texel, width, height, -)
+    const float4 *tri_tc;   // 2 x float4 per triangle, flat order: (u0,v0,u1,v1) (u2,v2,-,-)
+    const float4 *light_tc; // 2 x float4 per light: (u0,v0,u1,v1) (u2,v2,texture id bits,-)
     CameraDev cam;
 };
 
@@ -317,11 +323,32 @@ AKB_HD v3 closure_sample(const Bsdf &b, float ux, float uy, v3 wo, v3 &wi, float
 // Material::select_material + get_bsdf (kernel/material.h:255-297). u = ctx.u1[0], which MaterialEvalContext draws
 // from a COPY of the sampler (material.h:198-202), i.e. the same number the BSDF sample then uses as u.x.
 // Returns the leaf material index; choice_pdf accumulates 1/frac or 1/(1-frac) (sic: a multiplication, :260-268).
-AKB_HD int select_material(const akb_material *mats, int mat, float u, float &choice_pdf) {
+// ImageTexture::evaluate (kernel/texture.h:45-49) + TImage::operator()(float2) (core/image.hpp:46-68):
+// tc = fmod(texcoords, 1); tc.y = 1 - tc.y; texel int2(tc * resolution) (truncation), clamped to the image.
+AKB_HD v3 tex_lookup(const SceneDev &S, int tex, float tu, float tv) {
+    const int4 info = S.tex_info[tex];
+    const int first = info.x, w = info.y, h = info.z;
+    float x = fmodf(tu, 1.0f), y = fmodf(tv, 1.0f);
+    y = 1.0f - y;
+    int ix = (int)(x * (float)w), iy = (int)(y * (float)h);
+    ix = ix < 0 ? 0 : (ix > w - 1 ? w - 1 : ix);
+    iy = iy < 0 ? 0 : (iy > h - 1 ? h - 1 : iy);
+    const float4 t = AKB_LD4(S.texels + (size_t)first + (size_t)ix + (size_t)iy * (size_t)w);
+    return mk3(t.x, t.y, t.z);
+}
+// Triangle::texcoord(uv) = lerp3 of the corner texcoords (kernel/shape.h:40-42)
+AKB_HD void tri_texcoord(const float4 &a, const float4 &b, float u, float v, float &tu, float &tv) {
+    const v3 t = lerp3(mk3(a.x, a.y, 0.f), mk3(a.z, a.w, 0.f), mk3(b.x, b.y, 0.f), u, v);
+    tu = t.x, tv = t.y;
+}
+
+AKB_HD int select_material(const SceneDev &S, int mat, float u, float tu, float tv, float &choice_pdf) {
+    const akb_material *mats = S.mats;
     choice_pdf = 1.0f;
     int guard = 0;
     while (mats[mat].type == AKB_MAT_MIX && guard++ < 64) {
         float frac = mats[mat].fraction;
+        if (S.n_textures && mats[mat].fraction_tex >= 0) frac = tex_lookup(S, mats[mat].fraction_tex, tu, tv).x;
         if (u < frac) {
             u = u / frac;
             choice_pdf *= 1.0f / frac;
@@ -338,16 +365,18 @@ AKB_HD int closure_kind_of(int type) {
     return type == AKB_MAT_DIFFUSE ? CL_DIFFUSE
                                    : (type == AKB_MAT_GLOSSY ? CL_GGX : (type == AKB_MAT_DIELECTRIC ? CL_DIELECTRIC : CL_NULL));
 }
-AKB_HD Bsdf material_get_bsdf(const akb_material *mats, int mat, float u, v3 ns) {
+AKB_HD Bsdf material_get_bsdf(const SceneDev &S, int mat, float u, v3 ns, float tu, float tv) {
     Bsdf b;
-    int leaf = select_material(mats, mat, u, b.choice_pdf);
-    const akb_material &m = mats[leaf];
+    int leaf = select_material(S, mat, u, tu, tv, b.choice_pdf);
+    const akb_material &m = S.mats[leaf];
     b.frame = frame_make(ns);
     b.R = mk3(m.color[0], m.color[1], m.color[2]);
     b.kind = closure_kind_of(m.type);
+    if (S.n_textures && m.color_tex >= 0 && b.kind != CL_NULL) b.R = tex_lookup(S, m.color_tex, tu, tv);
     b.alpha = 0.f, b.ior = m.ior;
     if (b.kind == CL_GGX) {
         float r = m.roughness;
+        if (S.n_textures && m.roughness_tex >= 0) r = tex_lookup(S, m.roughness_tex, tu, tv).x;
         r *= r; // material.h:225-226
         b.alpha = r;
     }
@@ -406,10 +435,16 @@ AKB_HD int path_vertex(const SceneDev &S, PathState<SAMP> &ps, v3 ray_d, float h
     const akb_material &m = S.mats[mat];
     const v3 ng = mk3(s1.w, s2.w, AKB_LD4(sr + 3).w);
     const v3 wo = neg3(ray_d);
+    float tu = 0.f, tv = 0.f; // si.texcoords (kernel/interaction.h:40-42); only needed when the scene has image textures
+    if (S.n_textures) tri_texcoord(AKB_LD4(S.tri_tc + 2 * (size_t)tri), AKB_LD4(S.tri_tc + 2 * (size_t)tri + 1), hu, hv, tu, tv);
     if (m.type == AKB_MAT_EMISSIVE) { // :102-111
         if (ps.depth == 0) {
             bool face_front = dot3(neg3(wo), ng) < 0.0f;
-            if (m.double_sided || face_front) ps.L = add3(ps.L, mul3(ps.beta, mk3(m.color[0], m.color[1], m.color[2])));
+            if (m.double_sided || face_front) {
+                v3 Le = mk3(m.color[0], m.color[1], m.color[2]);
+                if (S.n_textures && m.color_tex >= 0) Le = tex_lookup(S, m.color_tex, tu, tv);
+                ps.L = add3(ps.L, mul3(ps.beta, Le));
+            }
         }
         return 0;
     }
@@ -420,7 +455,7 @@ AKB_HD int path_vertex(const SceneDev &S, PathState<SAMP> &ps, v3 ray_d, float h
     const v3 ns = lerp3(mk3(s3.x, s3.y, s3.z), mk3(s4.x, s4.y, s4.z), mk3(s5.x, s5.y, s5.z), hu, hv);
     float bux, buy;
     ps.rng.next2d(bux, buy);
-    const Bsdf bsdf = material_get_bsdf(S.mats, mat, bux, ns);
+    const Bsdf bsdf = material_get_bsdf(S, mat, bux, ns, tu, tv);
     const v3 wo_l = w2l(bsdf.frame, wo);
     v3 wi_l;
     float pdf;
@@ -455,7 +490,17 @@ AKB_HD int path_vertex(const SceneDev &S, PathState<SAMP> &ps, v3 ray_d, float h
         if (!(lpdf <= 0.0f)) { // :76
             light_pdf *= lpdf;
             const v3 fe = closure_evaluate(bsdf, w2l(bsdf.frame, wo), w2l(bsdf.frame, lwi));
-            const v3 ff = scale3(fabsf(dot3(ns, lwi)), mul3(mk3(l1.w, l2.w, l3.w), fe));
+            v3 Le = mk3(l1.w, l2.w, l3.w);
+            if (S.n_textures) { // sample.L = color->evaluate(triangle.texcoord(coords)), kernel/light.h:65
+                const float4 t0 = AKB_LD4(S.light_tc + 2 * (size_t)li), t1 = AKB_LD4(S.light_tc + 2 * (size_t)li + 1);
+                const int ltex = (int)akb_f2u(t1.z);
+                if (ltex >= 0) {
+                    float lu, lv;
+                    tri_texcoord(t0, t1, b0, b1, lu, lv);
+                    Le = tex_lookup(S, ltex, lu, lv);
+                }
+            }
+            const v3 ff = scale3(fabsf(dot3(ns, lwi)), mul3(Le, fe));
             const v3 color = div3s(mul3(ps.beta, ff), light_pdf);
             if (!is_black(color)) {
                 shadow.o = lp, shadow.d = neg3(lwi);

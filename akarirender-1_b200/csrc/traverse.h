@@ -38,6 +38,9 @@ struct float4 {
 struct uint2 {
     uint32_t x, y;
 };
+struct int4 {
+    int x, y, z, w;
+};
 #endif
 inline uint32_t akb_f2u(float f) {
     uint32_t u;

@@ -106,22 +106,49 @@ akb_camera camera_from(const Object &o) {
     return cam;
 }
 
-// resolve_texture (core/nodes/material.cpp:73-88): [r,g,b] | number | "image path"
-void texture_rgb(const Object &o, const char *field, const Value &v, float rgb[3]) {
-    if (v.is_array()) {
-        float_array(o, field, v, rgb, 3);
-    } else if (v.is_number()) {
-        rgb[0] = rgb[1] = rgb[2] = (float)v.num;
-    } else if (v.is_string()) {
-        bad(o, std::string("field ") + field + ": image textures (\"" + v.str + "\") are not supported by this backend yet; use a constant [r,g,b]");
-    } else {
-        bad(o, std::string("field ") + field + " must be [r,g,b], a number or an image path");
-    }
-}
-
 struct Flattener {
     SceneFile *sf;
     std::map<const Object *, int> index; // scene-wide material table, one entry per distinct node
+    std::map<std::string, int> texture_of; // image textures by resolved path
+
+    // ImageTextureNode + DefaultImageReader (core/nodes/material.cpp:46-71, core/image.cpp:105-123): bytes / 255.0f,
+    // alpha 1. The reference opens the path relative to the directory of the file being parsed.
+    int image_texture(const Object &o, const std::string &rel) {
+        const std::string path = join_path(dir_of(o.file), rel);
+        auto it = texture_of.find(path);
+        if (it != texture_of.end()) return it->second;
+        int w = 0, h = 0;
+        std::vector<uint8_t> rgb;
+        read_png_rgb8(path, &w, &h, &rgb);
+        auto tex = std::make_unique<std::vector<float>>((size_t)w * h * 4);
+        for (size_t i = 0; i < (size_t)w * h; i++) {
+            for (int k = 0; k < 3; k++) (*tex)[4 * i + k] = (float)rgb[3 * i + k] / 255.0f;
+            (*tex)[4 * i + 3] = 1.0f;
+        }
+        akb_texture d;
+        d.width = w, d.height = h, d.rgba = tex->data();
+        const int id = (int)sf->textures.size();
+        sf->textures.push_back(d);
+        sf->texels.push_back(std::move(tex));
+        texture_of[path] = id;
+        return id;
+    }
+
+    // resolve_texture (core/nodes/material.cpp:73-88): [r,g,b] | number | "image path". Returns the texture index
+    // (-1 for a constant, whose value goes to rgb).
+    int texture_rgb(const Object &o, const char *field, const Value &v, float rgb[3]) {
+        rgb[0] = rgb[1] = rgb[2] = 0.0f;
+        if (v.is_array()) {
+            float_array(o, field, v, rgb, 3);
+        } else if (v.is_number()) {
+            rgb[0] = rgb[1] = rgb[2] = (float)v.num;
+        } else if (v.is_string()) {
+            return image_texture(o, v.str);
+        } else {
+            bad(o, std::string("field ") + field + " must be [r,g,b], a number or an image path");
+        }
+        return -1;
+    }
 
     const Object &material_node(const Object &owner, const char *field, const Value &v) {
         if (!v.is_object()) bad(owner, std::string("field ") + field + " must be a material node");
@@ -138,26 +165,27 @@ struct Flattener {
         akb_material e;
         memset(&e, 0, sizeof e);
         e.child_a = e.child_b = -1;
+        e.color_tex = e.roughness_tex = e.fraction_tex = -1;
         sf->materials.push_back(e); // children are appended after their parent
         if (m.type == "DiffuseMaterial" || m.type == "EmissiveMaterial") {
             e.type = m.type == "DiffuseMaterial" ? AKB_MAT_DIFFUSE : AKB_MAT_EMISSIVE;
             const Value *c = m.find("color");
             if (!c) bad(m, "field color missing");
-            texture_rgb(m, "color", *c, e.color);
+            e.color_tex = texture_rgb(m, "color", *c, e.color);
         } else if (m.type == "GlossyMaterial") {
             e.type = AKB_MAT_GLOSSY;
             const Value *c = m.find("color"), *r = m.find("roughness");
             if (!c || !r) bad(m, "fields color and roughness are required");
-            texture_rgb(m, "color", *c, e.color);
+            e.color_tex = texture_rgb(m, "color", *c, e.color);
             float rr[3];
-            texture_rgb(m, "roughness", *r, rr);
+            e.roughness_tex = texture_rgb(m, "roughness", *r, rr);
             e.roughness = rr[0]; // kernel/material.h:225-226 reads channel 0
         } else if (m.type == "MixMaterial") {
             e.type = AKB_MAT_MIX;
             const Value *fr = m.find("fraction"), *a = m.find("first"), *b = m.find("second");
             if (!fr || !a || !b) bad(m, "fields fraction, first and second are required");
             float ff[3];
-            texture_rgb(m, "fraction", *fr, ff);
+            e.fraction_tex = texture_rgb(m, "fraction", *fr, ff);
             e.fraction = ff[0];
             e.child_a = material_index(material_node(m, "first", *a));
             e.child_b = material_index(material_node(m, "second", *b));
@@ -165,7 +193,8 @@ struct Flattener {
             e.type = AKB_MAT_DIELECTRIC;
             e.color[0] = e.color[1] = e.color[2] = 1.0f;
             e.ior = 1.5f;
-            if (const Value *c = m.find("color")) texture_rgb(m, "color", *c, e.color);
+            if (const Value *c = m.find("color"))
+                if (texture_rgb(m, "color", *c, e.color) >= 0) bad(m, "field color of a DielectricMaterial must be a constant");
             if (const Value *i = m.find("ior")) e.ior = (float)num(m, "ior", *i);
         } else {
             bad(m, "not a material node");
@@ -305,6 +334,7 @@ std::unique_ptr<SceneFile> load_scene_file(const std::string &path) {
     sf->desc.n_meshes = (uint32_t)sf->mesh_descs.size(), sf->desc.meshes = sf->mesh_descs.data();
     sf->desc.n_materials = (uint32_t)sf->materials.size(), sf->desc.materials = sf->materials.data();
     sf->desc.camera = camera_from(*cam->obj);
+    sf->desc.n_textures = (uint32_t)sf->textures.size(), sf->desc.textures = sf->textures.data();
     return sf;
 }
 

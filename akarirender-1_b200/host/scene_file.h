@@ -23,6 +23,8 @@ struct SceneFile {
     std::vector<std::unique_ptr<MeshData>> meshes;
     std::vector<akb_mesh> mesh_descs;
     std::vector<akb_material> materials;
+    std::vector<std::unique_ptr<std::vector<float>>> texels; // RGBA float per image texture
+    std::vector<akb_texture> textures;
     akb_scene_desc desc;
     akb_render_params params;
     std::string output = "out.png";
@@ -34,6 +36,10 @@ std::unique_ptr<SceneFile> load_scene_file(const std::string &path);
 
 // core/mesh.cpp:48-85
 void read_mesh_file(const std::string &path, MeshData *out);
+
+// 8-bit PNG -> tightly packed RGB bytes, the way `stbi_load(path, &x, &y, &channel, 3)` returns them
+// (core/image.cpp:105). png_read.cpp.
+void read_png_rgb8(const std::string &path, int *width, int *height, std::vector<uint8_t> *rgb);
 
 // core/image.cpp:38-61 writes 8-bit PNG through stb; here: a self-contained PNG encoder (stored deflate blocks) and a
 // float PFM dump of radiance/weight (the reference has no float output).

@@ -17,34 +17,121 @@ from . import abi
 F32 = np.float32
 
 
-# ---- materials (core/nodes/material.cpp:89-170) ------------------------------------------------------------
+# ---- textures + materials (core/nodes/material.cpp:25-170) ---------------------------------------------------
+class ImageTexture:
+    """ImageTextureNode (core/nodes/material.cpp:46-71): texels as the reference's reader stores them
+    (core/image.cpp:105-123: byte / 255.0f as float32, alpha 1). `rgba` is (H, W, 4) float32, top row first."""
+
+    def __init__(self, path=None, rgba=None):
+        self.path = path
+        if rgba is None:
+            rgb8 = read_png_rgb8(path)
+            rgba = np.ones(rgb8.shape[:2] + (4,), F32)
+            rgba[..., :3] = rgb8.astype(F32) / F32(255.0)
+        self.rgba = np.ascontiguousarray(rgba, F32)
+        assert self.rgba.ndim == 3 and self.rgba.shape[2] == 4
+
+    def rgb8(self):
+        return np.clip(np.rint(self.rgba[..., :3] * 255.0), 0, 255).astype(np.uint8)
+
+
+def read_png_rgb8(path):
+    """8-bit non-interlaced PNG -> (H, W, 3) uint8 (grey and alpha variants are expanded / dropped like stbi_load(..., 3))."""
+    import zlib
+    b = open(path, "rb").read()
+    assert b[:8] == b"\x89PNG\r\n\x1a\n", "not a PNG file"
+    o, idat, hdr = 8, b"", None
+    while o < len(b):
+        n, tag = struct.unpack(">I4s", b[o:o + 8])
+        if tag == b"IHDR":
+            hdr = struct.unpack(">IIBBBBB", b[o + 8:o + 8 + n])
+        elif tag == b"IDAT":
+            idat += b[o + 8:o + 8 + n]
+        o += 12 + n
+    w, h, depth, ctype, _, _, lace = hdr
+    assert depth == 8 and lace == 0 and ctype in (0, 2, 4, 6), "unsupported PNG variant"
+    ch = {0: 1, 2: 3, 4: 2, 6: 4}[ctype]
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, w * ch + 1)
+    out = np.zeros((h, w * ch), np.int32)
+    for y in range(h):
+        f, line = raw[y, 0], raw[y, 1:].astype(np.int32)
+        prev = out[y - 1] if y else np.zeros(w * ch, np.int32)
+        if f == 0:
+            cur = line
+        elif f == 2:
+            cur = (line + prev) & 255
+        else:
+            cur = np.zeros(w * ch, np.int32)
+            for i in range(w * ch):
+                a = cur[i - ch] if i >= ch else 0
+                c = prev[i - ch] if i >= ch else 0
+                if f == 1:
+                    pr = a
+                elif f == 3:
+                    pr = (a + prev[i]) >> 1
+                else:
+                    pa, pb, pc = abs(prev[i] - c), abs(a - c), abs(a + prev[i] - 2 * c)
+                    pr = a if pa <= pb and pa <= pc else (prev[i] if pb <= pc else c)
+                cur[i] = (line[i] + pr) & 255
+        out[y] = cur
+    px = out.reshape(h, w, ch).astype(np.uint8)
+    if ch <= 2:
+        return np.repeat(px[..., :1], 3, axis=2)
+    return px[..., :3].copy()
+
+
+def write_png_rgb8(path, rgb8):
+    import zlib
+    h, w = rgb8.shape[:2]
+    raw = b"".join(b"\x00" + rgb8[y].tobytes() for y in range(h))
+
+    def chunk(tag, body):
+        return struct.pack(">I", len(body)) + tag + body + struct.pack(">I", zlib.crc32(tag + body))
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 2, 0, 0, 0))
+                + chunk(b"IDAT", zlib.compress(raw, 6)) + chunk(b"IEND", b""))
+
+
 class MaterialNode:
     type = None
 
-    def entry(self, index_of):
+    def entry(self, index_of, tex_of):
         raise NotImplementedError
 
 
 def _rgb(v):
+    """A texture value as the scene language has it: [r,g,b] | number | ImageTexture (core/nodes/material.cpp:73-88)."""
+    if isinstance(v, ImageTexture):
+        return v
     if isinstance(v, (int, float)):
         return (float(v),) * 3
     return tuple(float(x) for x in v)
+
+
+def _const(v):
+    return (0.0, 0.0, 0.0) if isinstance(v, ImageTexture) else v
+
+
+def _mat(type_, color=(0, 0, 0), roughness=0.0, fraction=0.0, a=-1, b=-1, double_sided=0, ior=0.0, tex=(-1, -1, -1)):
+    return abi.Material(type_, (C.c_float * 3)(*color), roughness, fraction, a, b, double_sided, ior, *tex)
 
 
 class DiffuseMaterial(MaterialNode):
     def __init__(self, color):
         self.color = _rgb(color)
 
-    def entry(self, index_of):
-        return abi.Material(abi.MAT_DIFFUSE, (C.c_float * 3)(*self.color), 0, 0, -1, -1, 0, 0)
+    def entry(self, index_of, tex_of):
+        return _mat(abi.MAT_DIFFUSE, _const(self.color), tex=(tex_of(self.color), -1, -1))
 
 
 class GlossyMaterial(MaterialNode):
     def __init__(self, color, roughness):
-        self.color, self.roughness = _rgb(color), float(roughness)
+        self.color = _rgb(color)
+        self.roughness = roughness if isinstance(roughness, ImageTexture) else float(roughness)
 
-    def entry(self, index_of):
-        return abi.Material(abi.MAT_GLOSSY, (C.c_float * 3)(*self.color), self.roughness, 0, -1, -1, 0, 0)
+    def entry(self, index_of, tex_of):
+        r = 0.0 if isinstance(self.roughness, ImageTexture) else self.roughness
+        return _mat(abi.MAT_GLOSSY, _const(self.color), roughness=r, tex=(tex_of(self.color), tex_of(self.roughness), -1))
 
 
 class EmissiveMaterial(MaterialNode):
@@ -52,27 +139,28 @@ class EmissiveMaterial(MaterialNode):
         # the reference node never sets double_sided (core/nodes/material.cpp:152-155)
         self.color, self.double_sided = _rgb(color), bool(double_sided)
 
-    def entry(self, index_of):
-        return abi.Material(abi.MAT_EMISSIVE, (C.c_float * 3)(*self.color), 0, 0, -1, -1, int(self.double_sided), 0)
+    def entry(self, index_of, tex_of):
+        return _mat(abi.MAT_EMISSIVE, _const(self.color), double_sided=int(self.double_sided), tex=(tex_of(self.color), -1, -1))
 
 
 class MixMaterial(MaterialNode):
     def __init__(self, fraction, first, second):
-        self.fraction, self.first, self.second = float(fraction), first, second
+        self.fraction = fraction if isinstance(fraction, ImageTexture) else float(fraction)
+        self.first, self.second = first, second
 
-    def entry(self, index_of):
-        return abi.Material(abi.MAT_MIX, (C.c_float * 3)(0, 0, 0), 0, self.fraction, index_of(self.first),
-                            index_of(self.second), 0, 0)
+    def entry(self, index_of, tex_of):
+        f = 0.0 if isinstance(self.fraction, ImageTexture) else self.fraction
+        return _mat(abi.MAT_MIX, fraction=f, a=index_of(self.first), b=index_of(self.second), tex=(-1, -1, tex_of(self.fraction)))
 
 
 class DielectricMaterial(MaterialNode):
     """Extension: smooth dielectric; not present in the reference."""
 
     def __init__(self, color=(1, 1, 1), ior=1.5):
-        self.color, self.ior = _rgb(color), float(ior)
+        self.color, self.ior = tuple(float(x) for x in _rgb(color)), float(ior)
 
-    def entry(self, index_of):
-        return abi.Material(abi.MAT_DIELECTRIC, (C.c_float * 3)(*self.color), 0, 0, -1, -1, 0, self.ior)
+    def entry(self, index_of, tex_of):
+        return _mat(abi.MAT_DIELECTRIC, self.color, ior=self.ior)
 
 
 # ---- camera (core/nodes/camera.cpp:26-51) -------------------------------------------------------------------
@@ -266,20 +354,29 @@ def write_akari(scene, directory, name="scene.akari"):
     """Writes `scene` as a reference-format scene file + one .mesh per shape into `directory`. Returns the path."""
     import os
     os.makedirs(directory, exist_ok=True)
-    lines, names = [], {}
+    lines, names, tex_files = [], {}, {}
+
+    def tex(v):
+        """A texture slot's literal: [r,g,b] / number, or the path of a PNG written next to the scene file."""
+        if isinstance(v, ImageTexture):
+            if id(v) not in tex_files:
+                tex_files[id(v)] = "tex%d.png" % len(tex_files)
+                write_png_rgb8(os.path.join(directory, tex_files[id(v)]), v.rgb8())
+            return '"%s"' % tex_files[id(v)]
+        return _sdl_list(v) if isinstance(v, tuple) else sdl_number(v)
 
     def material(m):
         if id(m) in names:
             return names[id(m)]
         if isinstance(m, MixMaterial):
             a, b = material(m.first), material(m.second)
-            body = "MixMaterial { fraction: %s, first: $%s, second: $%s }" % (sdl_number(m.fraction), a, b)
+            body = "MixMaterial { fraction: %s, first: $%s, second: $%s }" % (tex(m.fraction), a, b)
         elif isinstance(m, DiffuseMaterial):
-            body = "DiffuseMaterial { color: %s }" % _sdl_list(m.color)
+            body = "DiffuseMaterial { color: %s }" % tex(m.color)
         elif isinstance(m, GlossyMaterial):
-            body = "GlossyMaterial { color: %s, roughness: %s }" % (_sdl_list(m.color), sdl_number(m.roughness))
+            body = "GlossyMaterial { color: %s, roughness: %s }" % (tex(m.color), tex(m.roughness))
         elif isinstance(m, EmissiveMaterial):
-            body = "EmissiveMaterial { color: %s }" % _sdl_list(m.color)
+            body = "EmissiveMaterial { color: %s }" % tex(m.color)
         elif isinstance(m, DielectricMaterial):
             body = "DielectricMaterial { color: %s, ior: %s }" % (_sdl_list(m.color), sdl_number(m.ior))
         else:
@@ -378,6 +475,16 @@ class Scene:
                     index_of(node.first), index_of(node.second)
             return ids[id(node)]
 
+        textures, tex_ids = [], {}
+
+        def tex_of(v):
+            if not isinstance(v, ImageTexture):
+                return -1
+            if id(v) not in tex_ids:
+                tex_ids[id(v)] = len(textures)
+                textures.append(v)
+            return tex_ids[id(v)]
+
         keep = []
         meshes = (abi.Mesh * len(self.shapes))()
         fp, ip = C.POINTER(C.c_float), C.POINTER(C.c_int32)
@@ -392,7 +499,7 @@ class Scene:
         mats = (abi.Material * max(1, len(table)))()
         i = 0
         while i < len(table):  # table may grow while Mix children are indexed
-            mats_entry = table[i].entry(index_of)
+            mats_entry = table[i].entry(index_of, tex_of)
             if len(table) > len(mats):
                 new = (abi.Material * len(table))()
                 for j in range(i):
@@ -405,5 +512,10 @@ class Scene:
         d.n_meshes, d.meshes = len(self.shapes), meshes
         d.n_materials, d.materials = len(table), mats
         d.camera = self.camera.desc()
-        keep += [meshes, mats]
+        texs = (abi.Texture * max(1, len(textures)))()
+        for i, t in enumerate(textures):
+            texs[i].height, texs[i].width = t.rgba.shape[:2]
+            texs[i].rgba = t.rgba.ctypes.data_as(fp)
+        d.n_textures, d.textures = len(textures), texs
+        keep += [meshes, mats, texs, textures]
         return d, keep

@@ -139,3 +139,35 @@ def mixed_box(resolution=(96, 96), spp=8, max_depth=5, **path_kw):
     mesh.materials[5] = mix  # short box
     mesh.materials[6] = nested  # tall box
     return sc
+
+
+def _checker(w, h, a, b, seed):
+    """Procedural test image: two-colour checker with per-texel noise, quantised to bytes like a decoded PNG."""
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:h, 0:w]
+    base = np.where(((xx // 2 + yy // 2) % 2)[..., None] == 0, np.array(a, F32), np.array(b, F32))
+    rgb8 = np.clip(np.rint((base + rng.uniform(-0.08, 0.08, base.shape)) * 255.0), 0, 255).astype(np.uint8)
+    rgba = np.ones((h, w, 4), F32)
+    rgba[..., :3] = rgb8.astype(F32) / F32(255.0)
+    return rgba
+
+
+def textured_box(resolution=(48, 48), spp=8, max_depth=5, **path_kw):
+    """Cornell geometry with an image texture in every texture slot the reference has (kernel/texture.h:39-57):
+    Diffuse.color, Glossy.color + roughness, Mix.fraction and Emissive.color; texcoords are stretched past [0,1] and
+    below 0 so that the fmod / flip / clamp rules of the lookup all matter."""
+    from .nodes import ImageTexture
+    sc = cornell_box(resolution, spp, max_depth, **path_kw)
+    mesh = sc.shapes[0]
+    mesh.texcoords = (mesh.texcoords.reshape(-1, 2) * np.array([2.5, 1.75], F32) - np.array([0.75, 0.4], F32)).reshape(-1).astype(F32)
+    floor = ImageTexture(rgba=_checker(16, 12, (0.8, 0.75, 0.7), (0.25, 0.3, 0.6), 1))
+    wall = ImageTexture(rgba=_checker(8, 8, (0.9, 0.9, 0.9), (0.6, 0.2, 0.2), 2))
+    rough = ImageTexture(rgba=_checker(5, 7, (0.2, 0.2, 0.2), (0.7, 0.7, 0.7), 3))
+    frac = ImageTexture(rgba=_checker(6, 4, (0.15, 0.5, 0.5), (0.85, 0.5, 0.5), 4))
+    glow = ImageTexture(rgba=_checker(4, 4, (1.0, 0.9, 0.6), (0.5, 0.2, 0.1), 5) * np.array([17, 17, 17, 1], F32))
+    mesh.materials[2] = DiffuseMaterial(floor)
+    mesh.materials[4] = GlossyMaterial(wall, rough)
+    mesh.materials[5] = MixMaterial(frac, DiffuseMaterial((0.2, 0.7, 0.3)), GlossyMaterial((0.9, 0.9, 0.9), 0.35))
+    mesh.materials[6] = MixMaterial(0.4, DiffuseMaterial(floor), GlossyMaterial(wall, 0.5))
+    mesh.materials[7] = EmissiveMaterial(glow)
+    return sc

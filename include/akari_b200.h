@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define AKB_ABI_VERSION 2
+#define AKB_ABI_VERSION 3
 
 typedef enum akb_status {
     AKB_OK = 0,
@@ -45,8 +45,16 @@ typedef enum akb_material_type {
     AKB_MAT_DIELECTRIC = 4
 } akb_material_type;
 
-/* One entry of the scene-wide material table. Textures are constant RGB (kernel/texture.h:30-37),
- * which is what every BASELINE config uses. */
+/* An image texture (kernel/texture.h:39-57): RGBA float texels, row-major, top row first, values as the reference's
+ * image reader stores them (core/image.cpp:105-123: byte / 255.0f, no transfer function; alpha unused).
+ * Lookup: tc = fmod(texcoords, 1); tc.y = 1 - tc.y; texel (int)(tc * resolution), clamped (core/image.hpp:46-68). */
+typedef struct akb_texture {
+    int32_t width, height;
+    const float *rgba; /* 4 * width * height */
+} akb_texture;
+
+/* One entry of the scene-wide material table. Every texture slot is a constant (kernel/texture.h:30-37) unless its
+ * *_tex index (into akb_scene_desc.textures) is >= 0, in which case the image texture replaces the constant. */
 typedef struct akb_material {
     int32_t type;         /* akb_material_type */
     float color[3];       /* Diffuse/Glossy reflectance, Emissive radiance, Dielectric tint */
@@ -56,6 +64,9 @@ typedef struct akb_material {
     int32_t child_b;      /* Mix: `second` -> material_B */
     int32_t double_sided; /* Emissive (core/nodes/material.cpp never sets it -> 0) */
     float ior;            /* Dielectric (extension) */
+    int32_t color_tex;     /* image texture for `color`, or -1 */
+    int32_t roughness_tex; /* Glossy: image texture for `roughness` (channel 0), or -1 */
+    int32_t fraction_tex;  /* Mix: image texture for `fraction` (channel 0), or -1 */
 } akb_material;
 
 /* One MeshInstance (kernel/instance.h:30-35); array layout = the .mesh file's (core/mesh.cpp:48-85). */
@@ -92,6 +103,9 @@ typedef struct akb_scene_desc {
     uint32_t _pad;
     const akb_material *materials;
     akb_camera camera;
+    uint32_t n_textures;
+    uint32_t _pad2;
+    const akb_texture *textures;
 } akb_scene_desc;
 
 /* ---- integrator parameters (kernel/integrators/gpu/integrator.h:39-53, core/nodes/integrator.cpp:26-84) */

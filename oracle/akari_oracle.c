@@ -164,6 +164,8 @@ typedef struct {
     v3 v[3];
     v3 color;
     float area_dummy;
+    float uv[3][2];
+    int32_t tex; /* image texture of the emissive colour, or -1 */
 } light_t;
 
 typedef struct oracle_scene {
@@ -173,6 +175,8 @@ typedef struct oracle_scene {
     uint32_t n_geoms;
     uint32_t n_mats;
     akb_material *mats;
+    uint32_t n_tex;
+    akb_texture *tex; /* deep copies */
     camera_t cam;
     /* lights: core/nodes/scene.cpp:51-92 ; Distribution1D: common/distribution.h:47-81 */
     uint32_t n_lights;
@@ -463,21 +467,43 @@ static v3 closure_sample(const bsdf_t *b, float ux, float uy, v3 wo, v3 *wi, flo
 
 /* Material::select_material + get_bsdf (kernel/material.h:255-297). u is ctx.u1[0] (drawn from a COPY of the
  * sampler, material.h:198-202). Emissive/null leaves give a null closure (get_bsdf0 returns BSDF()). */
-static bsdf_t material_get_bsdf(const oracle_scene *s, int32_t mat, float u, v3 ns) {
+/* ImageTexture::evaluate (kernel/texture.h:45-49) through TImage::operator()(float2) (core/image.hpp:46-68) */
+static v3 tex_eval(const oracle_scene *s, int32_t tex, float tu, float tv) {
+    const akb_texture *t = &s->tex[tex];
+    float x = fmodf(tu, 1.0f), y = fmodf(tv, 1.0f);
+    y = 1.0f - y;
+    int ix = (int)(x * (float)t->width), iy = (int)(y * (float)t->height);
+    if (ix < 0) ix = 0; if (ix > t->width - 1) ix = t->width - 1;
+    if (iy < 0) iy = 0; if (iy > t->height - 1) iy = t->height - 1;
+    const float *px = t->rgba + 4 * ((size_t)ix + (size_t)iy * (size_t)t->width);
+    return mk3(px[0], px[1], px[2]);
+}
+/* Triangle::texcoord(uv), kernel/shape.h:40-42 */
+static void tri_texcoord(const float uv[3][2], float u, float v, float *tu, float *tv) {
+    v3 t = lerp3v(mk3(uv[0][0], uv[0][1], 0.0f), mk3(uv[1][0], uv[1][1], 0.0f), mk3(uv[2][0], uv[2][1], 0.0f), u, v);
+    *tu = t.x; *tv = t.y;
+}
+
+static bsdf_t material_get_bsdf(const oracle_scene *s, int32_t mat, float u, v3 ns, float tu, float tv) {
     bsdf_t b; memset(&b, 0, sizeof b);
     float choice_pdf = 1.0f;
     const akb_material *m = &s->mats[mat];
     int guard = 0;
     while (m->type == AKB_MAT_MIX && guard++ < 64) {
-        float frac = m->fraction;
+        float frac = m->fraction_tex >= 0 ? tex_eval(s, m->fraction_tex, tu, tv).x : m->fraction;
         if (u < frac) { u = u / frac; m = &s->mats[m->child_b]; choice_pdf *= 1.0f / frac; }
         else { u = (u - frac) / (1.0f - frac); m = &s->mats[m->child_a]; choice_pdf *= 1.0f / (1.0f - frac); }
     }
     b.frame = frame_make(ns);
     b.choice_pdf = choice_pdf;
     b.R = mk3(m->color[0], m->color[1], m->color[2]);
+    if (m->color_tex >= 0 && (m->type == AKB_MAT_DIFFUSE || m->type == AKB_MAT_GLOSSY)) b.R = tex_eval(s, m->color_tex, tu, tv);
     if (m->type == AKB_MAT_DIFFUSE) b.kind = CL_DIFFUSE;
-    else if (m->type == AKB_MAT_GLOSSY) { b.kind = CL_GGX; float r = m->roughness; r *= r; b.alpha = r; }
+    else if (m->type == AKB_MAT_GLOSSY) {
+        b.kind = CL_GGX;
+        float r = m->roughness_tex >= 0 ? tex_eval(s, m->roughness_tex, tu, tv).x : m->roughness;
+        r *= r; b.alpha = r;
+    }
     else if (m->type == AKB_MAT_DIELECTRIC) { b.kind = CL_DIELECTRIC; b.ior = m->ior; }
     else b.kind = CL_NULL;
     return b;
@@ -518,12 +544,16 @@ static void run_path(const oracle_scene *s, path_t *pt, int px, int py, int rr_s
         v3 ns = lerp3v(tr->n[0], tr->n[1], tr->n[2], hu, hv);
         if (tr->mat < 0) break; /* reference dereferences null here; defined as "terminate" */
         const akb_material *mat = &s->mats[tr->mat];
+        float tu, tv; /* si.texcoords, kernel/interaction.h:40-42 */
+        tri_texcoord(tr->uv, hu, hv, &tu, &tv);
         /* on_surface_scatter, kernel/pathtracer.h:96-132 */
         if (mat->type == AKB_MAT_EMISSIVE) {
             if (pt->depth == 0) {
                 int face_front = dot3(neg3(wo), ng) < 0.0f;
-                if (mat->double_sided || face_front)
-                    pt->L = add3(pt->L, mul3(pt->beta, mk3(mat->color[0], mat->color[1], mat->color[2])));
+                if (mat->double_sided || face_front) {
+                    v3 Le = mat->color_tex >= 0 ? tex_eval(s, mat->color_tex, tu, tv) : mk3(mat->color[0], mat->color[1], mat->color[2]);
+                    pt->L = add3(pt->L, mul3(pt->beta, Le));
+                }
             }
             break;
         }
@@ -531,7 +561,7 @@ static void run_path(const oracle_scene *s, path_t *pt, int px, int py, int rr_s
         /* MaterialEvalContext draws from a copy: ctx.u1[0] == the x of the next2d() the BSDF sample uses */
         float bux, buy;
         next2d(&pt->smp, &bux, &buy);
-        bsdf_t bsdf = material_get_bsdf(s, tr->mat, bux, ns);
+        bsdf_t bsdf = material_get_bsdf(s, tr->mat, bux, ns, tu, tv);
         v3 wo_l = w2l(&bsdf.frame, wo), wi_l;
         float pdf;
         v3 f = closure_sample(&bsdf, bux, buy, wo_l, &wi_l, &pdf);
@@ -562,7 +592,13 @@ static void run_path(const oracle_scene *s, path_t *pt, int px, int py, int rr_s
             if (!(lpdf <= 0.0)) {
                 light_pdf *= lpdf;
                 v3 fe = closure_evaluate(&bsdf, w2l(&bsdf.frame, wo), w2l(&bsdf.frame, lwi));
-                v3 ff = scale3(fabsf(dot3(ns, lwi)), mul3(lt->color, fe));
+                v3 Le = lt->color;
+                if (lt->tex >= 0) { /* sample.L = color->evaluate(triangle.texcoord(coords)), kernel/light.h:65 */
+                    float lu, lv;
+                    tri_texcoord(lt->uv, b0, b1, &lu, &lv);
+                    Le = tex_eval(s, lt->tex, lu, lv);
+                }
+                v3 ff = scale3(fabsf(dot3(ns, lwi)), mul3(Le, fe));
                 v3 color = div3s(mul3(pt->beta, ff), light_pdf);
                 if (!is_black(color)) {
                     pt->n_shadow++;
@@ -614,6 +650,8 @@ static v3 ld3(const float *p) { return mk3(p[0], p[1], p[2]); }
 void akor_scene_destroy(oracle_scene *s) {
     if (!s) return;
     free(s->tris); free(s->geom_offset); free(s->mats); free(s->lights); free(s->func); free(s->cdf);
+    for (uint32_t i = 0; i < s->n_tex; i++) free((void *)s->tex[i].rgba);
+    free(s->tex);
     free(s->nodes); free(s->order); free(s);
 }
 
@@ -624,6 +662,18 @@ oracle_scene *akor_scene_create(const akb_scene_desc *d, int brute_force) {
     s->n_mats = d->n_materials;
     s->mats = (akb_material *)malloc(sizeof(akb_material) * (d->n_materials + 1));
     memcpy(s->mats, d->materials, sizeof(akb_material) * d->n_materials);
+    s->n_tex = d->n_textures;
+    s->tex = (akb_texture *)calloc(d->n_textures + 1, sizeof(akb_texture));
+    float *tex_integral = (float *)calloc(d->n_textures + 1, sizeof(float));
+    for (uint32_t i = 0; i < d->n_textures; i++) {
+        size_t n = (size_t)d->textures[i].width * d->textures[i].height;
+        float *px = (float *)malloc(16 * n);
+        memcpy(px, d->textures[i].rgba, 16 * n);
+        s->tex[i] = d->textures[i]; s->tex[i].rgba = px;
+        float I = 0; /* ImageTexture::integral, kernel/texture.h:50-56 */
+        for (size_t q = 0; q < n; q++) I += dot3(mk3(px[4 * q], px[4 * q + 1], px[4 * q + 2]), mk3((float)0.2126, (float)0.7152, (float)0.0722));
+        tex_integral[i] = I / (float)(d->textures[i].width * d->textures[i].height);
+    }
     s->n_geoms = d->n_meshes;
     s->geom_offset = (uint64_t *)malloc(sizeof(uint64_t) * (d->n_meshes + 1));
     uint64_t nt = 0;
@@ -662,8 +712,10 @@ oracle_scene *akor_scene_create(const akb_scene_desc *d, int brute_force) {
         l->v[0] = t->v[0]; l->v[1] = t->v[1]; l->v[2] = t->v[2];
         const float *c = s->mats[t->mat].color;
         l->color = mk3(c[0], c[1], c[2]);
+        l->tex = s->mats[t->mat].color_tex;
+        memcpy(l->uv, t->uv, sizeof l->uv);
         /* ConstantTexture::integral = luminance (kernel/texture.h:36, common/color.h:52-56) */
-        float I = dot3(l->color, mk3((float)0.2126, (float)0.7152, (float)0.0722));
+        float I = l->tex >= 0 ? tex_integral[l->tex] : dot3(l->color, mk3((float)0.2126, (float)0.7152, (float)0.0722));
         v3 tc[3];
         for (int j = 0; j < 3; j++) tc[j] = mk3(t->uv[j][0], t->uv[j][1], 0.0f);
         v3 tcc = cross3(sub3(tc[1], tc[0]), sub3(tc[2], tc[0]));
@@ -679,6 +731,7 @@ oracle_scene *akor_scene_create(const akb_scene_desc *d, int brute_force) {
     s->func_int = s->cdf[n_lights];
     if (s->func_int == 0) { for (uint32_t i = 1; i < n_lights + 1; i++) s->cdf[i] = (float)i / (float)n_lights; }
     else { for (uint32_t i = 1; i < n_lights + 1; i++) s->cdf[i] /= s->func_int; }
+    free(tex_integral);
     camera_init(&s->cam, &d->camera);
     if (!brute_force) build_accel(s);
     return s;

@@ -46,8 +46,18 @@ namespace {
             for (auto *m : materials)
                 ::operator delete(m);
         }
+        std::vector<std::vector<RGBA>> images; // texels of the description's image textures, as RGBAImage holds them
+        std::vector<int2> image_res;
         Texture<C> *tex(float r, float g, float b) {
             textures.emplace_back(new Texture<C>(ConstantTexture<C>(Spectrum(r, g, b))));
+            return textures.back().get();
+        }
+        // constant unless the description names an image texture: then the reference's ImageTexture over those texels
+        Texture<C> *tex(int image, float r, float g, float b) {
+            if (image < 0)
+                return tex(r, g, b);
+            RGBAImage::View view{images[image].data(), image_res[image]};
+            textures.emplace_back(new Texture<C>(ImageTexture<C>(view)));
             return textures.back().get();
         }
     };
@@ -74,7 +84,9 @@ namespace {
             auto &light = rs.lights[i];
             // Texture::integral() (kernel/texture.h:63-65) does not compile under g++ 13 (dependent-base lookup);
             // every texture here is constant, so call ConstantTexture::integral (kernel/texture.h:36) directly.
-            auto I = light.color->template get<ConstantTexture<C>>()->integral();
+            Float I = light.color->template isa<ImageTexture<C>>()
+                          ? light.color->template get<ImageTexture<C>>()->integral()
+                          : light.color->template get<ConstantTexture<C>>()->integral();
             auto &triangle = light.triangle;
             Float3 tc[3];
             for (int j = 0; j < 3; j++)
@@ -103,6 +115,14 @@ void *akref_scene_create(const akb_scene_desc *d) {
         }
         set_device_cpu(); // cmd/akari.cpp:41-76 does this before anything allocates (default_resource())
         auto rs = std::make_unique<RefScene>();
+        for (uint32_t i = 0; i < d->n_textures; i++) {
+            const akb_texture &t = d->textures[i];
+            std::vector<RGBA> px((size_t)t.width * t.height);
+            for (size_t k = 0; k < px.size(); k++)
+                px[k] = RGBA(float3(t.rgba[4 * k], t.rgba[4 * k + 1], t.rgba[4 * k + 2]), t.rgba[4 * k + 3]);
+            rs->images.push_back(std::move(px));
+            rs->image_res.push_back(int2(t.width, t.height));
+        }
         // materials: allocate raw storage first so Mix children can point at any entry
         rs->materials.resize(d->n_materials, nullptr);
         for (uint32_t i = 0; i < d->n_materials; i++)
@@ -111,15 +131,15 @@ void *akref_scene_create(const akb_scene_desc *d) {
             const akb_material &m = d->materials[i];
             switch (m.type) {
             case AKB_MAT_DIFFUSE:
-                new (rs->materials[i]) Material<C>(DiffuseMaterial<C>(rs->tex(m.color[0], m.color[1], m.color[2])));
+                new (rs->materials[i]) Material<C>(DiffuseMaterial<C>(rs->tex(m.color_tex, m.color[0], m.color[1], m.color[2])));
                 break;
             case AKB_MAT_GLOSSY:
-                new (rs->materials[i]) Material<C>(GlossyMaterial<C>(rs->tex(m.color[0], m.color[1], m.color[2]),
-                                                                     rs->tex(m.roughness, m.roughness, m.roughness)));
+                new (rs->materials[i]) Material<C>(GlossyMaterial<C>(rs->tex(m.color_tex, m.color[0], m.color[1], m.color[2]),
+                                                                     rs->tex(m.roughness_tex, m.roughness, m.roughness, m.roughness)));
                 break;
             case AKB_MAT_EMISSIVE:
                 new (rs->materials[i])
-                    Material<C>(EmissiveMaterial<C>(rs->tex(m.color[0], m.color[1], m.color[2]), m.double_sided != 0));
+                    Material<C>(EmissiveMaterial<C>(rs->tex(m.color_tex, m.color[0], m.color[1], m.color[2]), m.double_sided != 0));
                 break;
             case AKB_MAT_MIX:
                 if (m.child_a < 0 || m.child_b < 0 || (uint32_t)m.child_a >= d->n_materials ||
@@ -127,7 +147,7 @@ void *akref_scene_create(const akb_scene_desc *d) {
                     g_err = "mix child out of range";
                     return nullptr;
                 }
-                new (rs->materials[i]) Material<C>(MixMaterial<C>(rs->tex(m.fraction, m.fraction, m.fraction),
+                new (rs->materials[i]) Material<C>(MixMaterial<C>(rs->tex(m.fraction_tex, m.fraction, m.fraction, m.fraction),
                                                                   rs->materials[m.child_a], rs->materials[m.child_b]));
                 break;
             default:

@@ -116,6 +116,9 @@ void *hc_scene_create(const akb_scene_desc *d, int threads) {
     S.lights = (const float4 *)hs.lights.data();
     S.light_cdf = hs.light_cdf.data(), S.light_func = hs.light_func.data();
     S.light_func_int = hs.light_func_int, S.n_lights = (int)hs.light_func.size(), S.n_mats = (int)hs.mats.size();
+    S.n_textures = (int)(hs.tex_info.size() / 4);
+    S.texels = (const float4 *)hs.texels.data(), S.tex_info = (const int4 *)hs.tex_info.data();
+    S.tri_tc = (const float4 *)hs.tri_tc.data(), S.light_tc = (const float4 *)hs.light_tc.data();
     S.cam = hs.cam;
     return h;
 }

@@ -154,7 +154,7 @@ def test_parser_grammar(tmp_path):
         "export scene = DiffuseMaterial { color: 1 }\n": "not a Scene",
         "export scene = Scene { camera: PerspectiveCamera {}, integrator: Path {}, shapes: [ DiffuseMaterial { color: 1 } ] }\n": "AkariMesh",
         'export scene = Scene { camera: PerspectiveCamera {}, integrator: Path {}, shapes: [ AkariMesh { path: "none.mesh" } ] }\n': "none.mesh",
-        'export scene = Scene { camera: PerspectiveCamera {}, integrator: Path {}, shapes: [ AkariMesh { path: "shape0.mesh", materials: [ DiffuseMaterial { color: "tex.png" } ] } ] }\n': "image textures",
+        'export scene = Scene { camera: PerspectiveCamera {}, integrator: Path {}, shapes: [ AkariMesh { path: "shape0.mesh", materials: [ DiffuseMaterial { color: "tex.png" } ] } ] }\n': "tex.png: cannot open",
     }
     for text, needle in bad.items():
         (tmp_path / "bad.akari").write_text(text)
