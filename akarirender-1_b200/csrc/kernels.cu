@@ -407,7 +407,7 @@ __global__ void __launch_bounds__(kBlock) wf_trace_kernel(SceneDev S, RenderConf
     }
 }
 
-template <int SAMP>
+template <int SAMP, bool TEX>
 __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
     Counters *ctr = ws.ctr;
     // Work list: with material sorting the kNumKeys keyed queues, each padded to a warp so that warps are
@@ -449,7 +449,7 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
                 ps.beta = xyz(bd), ps.depth = __float_as_int(bd.w);
                 RaySeg next, sh;
                 v3 sc;
-                const int fl = path_vertex<SAMP>(S, ps, xyz(rd), hrec.x, hrec.y, tri, rc.max_depth, rc.rr_start, next, sh, sc);
+                const int fl = path_vertex<SAMP>(S, ps, xyz(rd), hrec.x, hrec.y, tri, rc.max_depth, rc.rr_start, next, sh, sc, TEX);
                 bool cont = (fl & VTX_CONTINUE) != 0;
                 const bool shadow = (fl & VTX_SHADOW) != 0;
                 // A ray leaving a vertex at depth == max_depth can never contribute (kernel/pathtracer.h:102-112: no
@@ -599,12 +599,19 @@ cudaError_t launch_wf_trace(const SceneDev &S, const RenderConfig &rc, const Wor
 
 cudaError_t launch_wf_shade(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int parity, int n_sms,
                             cudaStream_t st) {
-    static int occ_l = blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_LCG>, kBlock),
-               occ_p = blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_PCG>, kBlock);
-    if (rc.sampler == AKB_SAMPLER_PCG)
-        wf_shade_kernel<AKB_SAMPLER_PCG><<<n_sms * occ_p, kBlock, 0, st>>>(S, rc, ws, parity);
+    // four instantiations: sampler x (scene has image textures)
+    static int occ[2][2] = {{blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_LCG, false>, kBlock), blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_LCG, true>, kBlock)},
+                            {blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_PCG, false>, kBlock), blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_PCG, true>, kBlock)}};
+    const bool pcg = rc.sampler == AKB_SAMPLER_PCG, tex = S.n_textures > 0;
+    const int grid = n_sms * occ[pcg][tex];
+    if (pcg && tex)
+        wf_shade_kernel<AKB_SAMPLER_PCG, true><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+    else if (pcg)
+        wf_shade_kernel<AKB_SAMPLER_PCG, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+    else if (tex)
+        wf_shade_kernel<AKB_SAMPLER_LCG, true><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
     else
-        wf_shade_kernel<AKB_SAMPLER_LCG><<<n_sms * occ_l, kBlock, 0, st>>>(S, rc, ws, parity);
+        wf_shade_kernel<AKB_SAMPLER_LCG, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
     return cudaGetLastError();
 }
 

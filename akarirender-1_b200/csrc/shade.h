@@ -342,13 +342,13 @@ AKB_HD void tri_texcoord(const float4 &a, const float4 &b, float u, float v, flo
     tu = t.x, tv = t.y;
 }
 
-AKB_HD int select_material(const SceneDev &S, int mat, float u, float tu, float tv, float &choice_pdf) {
+AKB_HD int select_material(const SceneDev &S, int mat, float u, float tu, float tv, float &choice_pdf, bool tex_on = true) {
     const akb_material *mats = S.mats;
     choice_pdf = 1.0f;
     int guard = 0;
     while (mats[mat].type == AKB_MAT_MIX && guard++ < 64) {
         float frac = mats[mat].fraction;
-        if (S.n_textures && mats[mat].fraction_tex >= 0) frac = tex_lookup(S, mats[mat].fraction_tex, tu, tv).x;
+        if (tex_on && S.n_textures && mats[mat].fraction_tex >= 0) frac = tex_lookup(S, mats[mat].fraction_tex, tu, tv).x;
         if (u < frac) {
             u = u / frac;
             choice_pdf *= 1.0f / frac;
@@ -365,18 +365,18 @@ AKB_HD int closure_kind_of(int type) {
     return type == AKB_MAT_DIFFUSE ? CL_DIFFUSE
                                    : (type == AKB_MAT_GLOSSY ? CL_GGX : (type == AKB_MAT_DIELECTRIC ? CL_DIELECTRIC : CL_NULL));
 }
-AKB_HD Bsdf material_get_bsdf(const SceneDev &S, int mat, float u, v3 ns, float tu, float tv) {
+AKB_HD Bsdf material_get_bsdf(const SceneDev &S, int mat, float u, v3 ns, float tu, float tv, bool tex_on = true) {
     Bsdf b;
-    int leaf = select_material(S, mat, u, tu, tv, b.choice_pdf);
+    int leaf = select_material(S, mat, u, tu, tv, b.choice_pdf, tex_on);
     const akb_material &m = S.mats[leaf];
     b.frame = frame_make(ns);
     b.R = mk3(m.color[0], m.color[1], m.color[2]);
     b.kind = closure_kind_of(m.type);
-    if (S.n_textures && m.color_tex >= 0 && b.kind != CL_NULL) b.R = tex_lookup(S, m.color_tex, tu, tv);
+    if (tex_on && S.n_textures && m.color_tex >= 0 && b.kind != CL_NULL) b.R = tex_lookup(S, m.color_tex, tu, tv);
     b.alpha = 0.f, b.ior = m.ior;
     if (b.kind == CL_GGX) {
         float r = m.roughness;
-        if (S.n_textures && m.roughness_tex >= 0) r = tex_lookup(S, m.roughness_tex, tu, tv).x;
+        if (tex_on && S.n_textures && m.roughness_tex >= 0) r = tex_lookup(S, m.roughness_tex, tu, tv).x;
         r *= r; // material.h:225-226
         b.alpha = r;
     }
@@ -427,7 +427,9 @@ enum { VTX_CONTINUE = 1, VTX_SHADOW = 2 };
 // SHADOW -> `shadow` must be tested with occlude() and `shadow_color` added to L when it is unoccluded.
 template <int SAMP>
 AKB_HD int path_vertex(const SceneDev &S, PathState<SAMP> &ps, v3 ray_d, float hu, float hv, int tri, int max_depth,
-                       int rr_start, RaySeg &next, RaySeg &shadow, v3 &shadow_color) {
+                       int rr_start, RaySeg &next, RaySeg &shadow, v3 &shadow_color, const bool tex_on = true) {
+    // tex_on: a compile-time false in the kernel instantiation used for scenes without image textures (every BASELINE
+    // config), so that none of the texture code is even present there
     const float4 *sr = S.shading + 6 * (size_t)tri;
     const float4 s0 = AKB_LD4(sr), s1 = AKB_LD4(sr + 1), s2 = AKB_LD4(sr + 2);
     const int mat = (int)akb_f2u(s0.w);
@@ -436,13 +438,13 @@ AKB_HD int path_vertex(const SceneDev &S, PathState<SAMP> &ps, v3 ray_d, float h
     const v3 ng = mk3(s1.w, s2.w, AKB_LD4(sr + 3).w);
     const v3 wo = neg3(ray_d);
     float tu = 0.f, tv = 0.f; // si.texcoords (kernel/interaction.h:40-42); only needed when the scene has image textures
-    if (S.n_textures) tri_texcoord(AKB_LD4(S.tri_tc + 2 * (size_t)tri), AKB_LD4(S.tri_tc + 2 * (size_t)tri + 1), hu, hv, tu, tv);
+    if (tex_on && S.n_textures) tri_texcoord(AKB_LD4(S.tri_tc + 2 * (size_t)tri), AKB_LD4(S.tri_tc + 2 * (size_t)tri + 1), hu, hv, tu, tv);
     if (m.type == AKB_MAT_EMISSIVE) { // :102-111
         if (ps.depth == 0) {
             bool face_front = dot3(neg3(wo), ng) < 0.0f;
             if (m.double_sided || face_front) {
                 v3 Le = mk3(m.color[0], m.color[1], m.color[2]);
-                if (S.n_textures && m.color_tex >= 0) Le = tex_lookup(S, m.color_tex, tu, tv);
+                if (tex_on && S.n_textures && m.color_tex >= 0) Le = tex_lookup(S, m.color_tex, tu, tv);
                 ps.L = add3(ps.L, mul3(ps.beta, Le));
             }
         }
@@ -455,7 +457,7 @@ AKB_HD int path_vertex(const SceneDev &S, PathState<SAMP> &ps, v3 ray_d, float h
     const v3 ns = lerp3(mk3(s3.x, s3.y, s3.z), mk3(s4.x, s4.y, s4.z), mk3(s5.x, s5.y, s5.z), hu, hv);
     float bux, buy;
     ps.rng.next2d(bux, buy);
-    const Bsdf bsdf = material_get_bsdf(S, mat, bux, ns, tu, tv);
+    const Bsdf bsdf = material_get_bsdf(S, mat, bux, ns, tu, tv, tex_on);
     const v3 wo_l = w2l(bsdf.frame, wo);
     v3 wi_l;
     float pdf;
@@ -491,7 +493,7 @@ AKB_HD int path_vertex(const SceneDev &S, PathState<SAMP> &ps, v3 ray_d, float h
             light_pdf *= lpdf;
             const v3 fe = closure_evaluate(bsdf, w2l(bsdf.frame, wo), w2l(bsdf.frame, lwi));
             v3 Le = mk3(l1.w, l2.w, l3.w);
-            if (S.n_textures) { // sample.L = color->evaluate(triangle.texcoord(coords)), kernel/light.h:65
+            if (tex_on && S.n_textures) { // sample.L = color->evaluate(triangle.texcoord(coords)), kernel/light.h:65
                 const float4 t0 = AKB_LD4(S.light_tc + 2 * (size_t)li), t1 = AKB_LD4(S.light_tc + 2 * (size_t)li + 1);
                 const int ltex = (int)akb_f2u(t1.z);
                 if (ltex >= 0) {
