@@ -30,13 +30,14 @@ inline float half_area(const float *lo, const float *hi) {
 }
 
 constexpr int kBins = 16;
-constexpr int kMaxLeaf = 3;       // a CWBVH leaf slot addresses at most 3 triangles (unary-coded count)
 // Cost-model constants, overridable for tuning runs (AKB_BVH_TRAV_COST / AKB_BVH_PRIM_COST); see profiles/ for the sweep.
 static float env_float(const char *name, float dflt) {
     const char *e = getenv(name);
     return e && *e ? (float)atof(e) : dflt;
 }
 static const float kTraversalCost = env_float("AKB_BVH_TRAV_COST", 0.5f);
+// a CWBVH leaf slot addresses at most 3 triangles (unary-coded count); AKB_BVH_MAX_LEAF=1..3 for tuning runs
+static const int kMaxLeaf = std::min(3, std::max(1, (int)env_float("AKB_BVH_MAX_LEAF", 3.0f)));
 
 struct Builder {
     const float *lo, *hi; // padded triangle boxes
