@@ -286,10 +286,12 @@ def main():
             n_launch = max(1, (stp.n_kernel_launches - 2) // 2)
             bytes_total = BYTES_CLOSEST * stp.n_closest_rays + BYTES_ANY * stp.n_shadow_rays
             achieved = bytes_total / (stp.ms_extend * 1e-3) / 1e9 if stp.ms_extend > 0 else None
-            traffic = None
+            traffic, counters = None, {}
             try:
                 with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-                    traffic = json.load(f).get("wf_trace_dram_bytes_per_launch")
+                    tj = json.load(f)
+                traffic = 2 * tj["wf_trace_dram_bytes_per_half_frame_launch"]  # the capture is one of two half-frame launches
+                counters = {k[len("wf_trace_"):]: v for k, v in tj.items() if k.startswith("wf_trace_") and k.endswith(("_pct", "_instruction", "_of_peak"))}
             except Exception:
                 pass
             roof = {"bound": "hbm", "kernel": "wf_trace_kernel (closest-hit + any-hit CWBVH traversal)",
@@ -298,8 +300,10 @@ def main():
                     "avg_launch_ms": stp.ms_extend / n_launch, "bytes_per_launch": bytes_total / n_launch,
                     "kernel_share_of_step": stp.ms_extend / stp.ms_total, "shade_share_of_step": stp.ms_shade / stp.ms_total,
                     "mrays_per_s_in_kernel": (stp.n_closest_rays + stp.n_shadow_rays) / (stp.ms_extend * 1e-3) / 1e6,
+                    "ncu_counters": counters, "ncu_source": "profiles/r01f_wf_full.md",
                     "note": "BVH traversal is latency/issue/L2-bound, not HBM-streaming-bound; the HBM fraction is low by "
-                            "construction (SURVEY.md §8d) - see profiles/ for issue-slot and L2 figures"}
+                            "construction (SURVEY.md §8d): ncu_counters carries the issue-slot / pipe / lane figures of the "
+                            "same kernel"}
         extras = {}
         if not a.no_extras and world == 1:
             extras = ray_microbench(pkg, be, torch)
