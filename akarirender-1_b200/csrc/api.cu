@@ -255,6 +255,12 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
     S.light_func_int = hs.light_func_int;
     S.n_lights = (int)hs.light_func.size();
     S.n_mats = (int)hs.mats.size();
+    // if-if traversal for real trees, fused step for tiny ones (AKB_TRAV_IFIF=0/1 forces either; tuning aid)
+    {
+        const char *e = getenv("AKB_TRAV_IFIF");
+        const bool ifif = e ? e[0] == '1' : hs.bvh.nodes.size() >= 64;
+        S.trav_post_limit = ifif ? std::max(0, kStackSize - hs.bvh.depth - 1) : -1;
+    }
     S.n_textures = (int)(hs.tex_info.size() / 4);
     S.cam = hs.cam;
     sc->n_tris = hs.n_tris, sc->n_nodes = hs.bvh.nodes.size(), sc->bvh_bytes = hs.bvh.nodes.size() * sizeof(Node8);

@@ -62,11 +62,11 @@ __global__ void selftest_kernel(int *result, float a, float b, float c) {
 //   Src::load(i, T, tag)  -> true: T initialised for item i; false: the item needs no traversal (result ready)
 //   Src::complete(have, i, tag, T): called by all 32 lanes together; lanes with have == true consume their result
 __constant__ int c_fetch_chunk = 0; // 0: reserve exactly the idle-lane count per refill; >0: warp-private chunks (AKB_FETCH_CHUNK)
-__constant__ int c_refill_below = 20; // tunable at init (AKB_REFILL_BELOW); 20 measured best on B200
+__constant__ int c_refill_below = 0; // > 0: AKB_REFILL_BELOW override; else 24 with the if-if step, 20 with the fused one (measured best on B200)
 
 template <class Src>
 __device__ __forceinline__ void persistent_trace(const float4 *__restrict__ nodes, const float4 *__restrict__ tris, Src &src,
-                                                 uint32_t total, uint32_t *cursor) {
+                                                 uint32_t total, uint32_t *cursor, int post_limit) {
     const unsigned lane = threadIdx.x & 31;
     uint2 stack[kStackSize];
     Trav T;
@@ -75,7 +75,7 @@ __device__ __forceinline__ void persistent_trace(const float4 *__restrict__ node
     uint32_t item = 0, tag = 0;
     uint32_t w_next = 0, w_end = 0; // warp-private reserved range of the queue (one atomic per kFetchChunk items)
     bool drained = false;           // the global cursor has passed the end
-    const int refill_below = c_refill_below;
+    const int refill_below = c_refill_below > 0 ? c_refill_below : (post_limit >= 0 ? 24 : 20);
     const uint32_t fetch_chunk = (uint32_t)c_fetch_chunk;
     for (;;) {
         src.complete(have, item, tag, T);
@@ -112,7 +112,10 @@ __device__ __forceinline__ void persistent_trace(const float4 *__restrict__ node
         // lanes wait - was measured on B200 and did not pay: the node block then runs with fewer lanes (20 instead of
         // 26 of 32) and total issued instructions stay within 5 %; profiles/r01c_notes.md.)
         do {
-            if (active && trav_step(T, nodes, tris, stack)) active = false, have = true;
+            // post_limit >= 0: the "if-if" step (one node visit + one triangle test per lane and iteration, traverse.h);
+            // < 0: the fused step, which is better for tiny trees where a ray is a handful of steps
+            if (post_limit >= 0 ? trav_step_ii(T, nodes, tris, stack, active, post_limit) : (active && trav_step(T, nodes, tris, stack)))
+                active = false, have = true;
             act = __ballot_sync(0xffffffffu, active);
         } while (act != 0 && (no_more || __popc(act) >= refill_below));
     }
@@ -151,7 +154,7 @@ __global__ void __launch_bounds__(kBlock)
     trace_batch_kernel(SceneDev S, const float4 *__restrict__ org, const float4 *__restrict__ dir, uint32_t n, int any_hit,
                        akb_hit *__restrict__ hits, int32_t *__restrict__ occ, uint32_t *cursor) {
     BatchSrc src{org, dir, S.shading, hits, occ, any_hit != 0};
-    persistent_trace(S.nodes, S.tris, src, n, cursor);
+    persistent_trace(S.nodes, S.tris, src, n, cursor, S.trav_post_limit);
 }
 
 __global__ void generate_rays_kernel(SceneDev S, const int32_t *xy, const float *u2, size_t n, float4 *org, float4 *dir) {
@@ -397,7 +400,7 @@ __global__ void __launch_bounds__(kBlock) wf_trace_kernel(SceneDev S, RenderConf
     Counters *ctr = ws.ctr;
     const uint32_t n_ext = ctr->n_ext[b], n_sh = ctr->n_sh[b];
     WfSrc<SAMP> src{S, rc, ws, b, n_ext};
-    persistent_trace(S.nodes, S.tris, src, n_ext + n_sh, &ctr->fetch_trace);
+    persistent_trace(S.nodes, S.tris, src, n_ext + n_sh, &ctr->fetch_trace, S.trav_post_limit);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         // queues the NEXT shade step fills must start empty; nobody else touches them during this launch
         ctr->n_ext[b ^ 1] = 0;

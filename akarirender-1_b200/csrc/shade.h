@@ -89,6 +89,7 @@ struct SceneDev {
     float light_func_int;
     int n_lights;
     int n_mats;
+    int trav_post_limit; // traversal stack height below which a leftover triangle group may be parked (trav_step_ii)
     // image textures (kernel/texture.h:39-57); n_textures == 0 for every BASELINE config, and then none of this is read
     int n_textures;
     const float4 *texels;   // all textures back to back, RGBA
