@@ -164,6 +164,35 @@ int hc_trace(void *hv, const float *org, const float *dir, size_t n, int any_hit
     });
     return 0;
 }
+// the same, through the if-if step (trav_step_ii) the persistent warps use on real trees; post_limit < 0 = the value
+// api.cu derives (stack size - tree depth - 1); small values force the "finish the group in place" path
+int hc_trace_ii(void *hv, const float *org, const float *dir, size_t n, int any_hit, int post_limit, akb_hit *hits, int32_t *occ) {
+    HC *h = (HC *)hv;
+    const SceneDev &S = h->dev;
+    if (post_limit < 0) post_limit = std::max(0, kStackSize - h->hs.bvh.depth - 1);
+    for (size_t i = 0; i < n; i++) {
+        Trav T;
+        uint2 stack[kStackSize];
+        trav_init(T, mk3(org[4 * i], org[4 * i + 1], org[4 * i + 2]), mk3(dir[4 * i], dir[4 * i + 1], dir[4 * i + 2]), org[4 * i + 3],
+                  dir[4 * i + 3], any_hit != 0);
+        while (!trav_step_ii(T, S.nodes, S.tris, stack, true, post_limit)) {
+        }
+        if (any_hit) {
+            occ[i] = T.hit.tri >= 0 ? 1 : 0;
+        } else {
+            akb_hit r;
+            if (T.hit.tri >= 0) {
+                const float4 *sr = S.shading + 6 * (size_t)T.hit.tri;
+                r.t = T.hit.t, r.u = T.hit.u, r.v = T.hit.v;
+                r.geom_id = (int)akb_f2u(sr[4].w), r.prim_id = (int)akb_f2u(sr[5].w);
+            } else {
+                r.t = INFINITY, r.u = r.v = 0, r.prim_id = r.geom_id = -1;
+            }
+            hits[i] = r;
+        }
+    }
+    return 0;
+}
 int hc_generate_rays(void *hv, const int32_t *xy, const float *u2, size_t n, float *org, float *dir) {
     const SceneDev &S = ((HC *)hv)->dev;
     for (size_t i = 0; i < n; i++) {

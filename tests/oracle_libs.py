@@ -166,6 +166,18 @@ class HostCheck(_Base):
         keys = ["n_triangles", "n_bvh_nodes", "bvh_bytes", "n_lights", "triangle_bytes", "bvh_depth", "build_us"]
         return {k: int(self.lib.hc_info(self.h, i)) for i, k in enumerate(keys)}
 
+    def trace_ii(self, org_tmin, dir_tmax, any_hit=False, post_limit=-1):
+        """The same rays through the if-if traversal step (traverse.h trav_step_ii)."""
+        org = np.ascontiguousarray(org_tmin, np.float32)
+        dr = np.ascontiguousarray(dir_tmax, np.float32)
+        n = org.shape[0]
+        hits = np.zeros(n, dtype=HIT_DTYPE)
+        occ = np.zeros(n, np.int32)
+        rc = self.lib.hc_trace_ii(self.h, _ptr(org), _ptr(dr), C.c_size_t(n), C.c_int(int(any_hit)), C.c_int(post_limit),
+                                  _ptr(hits), _ptr(occ))
+        assert rc == 0
+        return occ if any_hit else hits
+
     def render(self, params, threads=0):
         film = np.zeros((self.height, self.width, 4), np.float32)
         rc = self.lib.hc_render(self.h, C.byref(params), _ptr(film), C.c_int(threads or os.cpu_count()))

@@ -96,6 +96,31 @@ def test_films_golden(G, S, mode):
         be.close()
 
 
+@pytest.mark.parametrize("name", ["cornell", "terrain"])
+def test_both_traversal_steps_bit_identical(G, S, name):
+    """The persistent warps pick the if-if step for real trees and the fused step for tiny ones (api.cu); forcing
+    either (AKB_TRAV_IFIF, read at scene creation) must give the same hits, occlusion flags and film bits."""
+    sc = S[name]
+    out = []
+    old = os.environ.get("AKB_TRAV_IFIF")
+    try:
+        for force in ("0", "1"):
+            os.environ["AKB_TRAV_IFIF"] = force
+            be = backend(sc)
+            h = be.trace(G[f"{name}_org2"], G[f"{name}_dir2"])
+            occ = be.trace(G[f"{name}_org2"], G[f"{name}_dir2_any"], any_hit=True)
+            film = be.render(sc.integrator.params())[0]
+            out.append((h.tobytes(), occ.tobytes(), film.tobytes()))
+            be.close()
+    finally:
+        if old is None:
+            os.environ.pop("AKB_TRAV_IFIF", None)
+        else:
+            os.environ["AKB_TRAV_IFIF"] = old
+    assert out[0] == out[1]
+    assert np.array_equal(np.frombuffer(out[0][1], np.int32), G[f"{name}_occ2"])
+
+
 def test_wavefront_equals_megakernel_and_sorting_is_neutral():
     sc = scenes.mixed_box((80, 56), 6, 5)
     be = backend(sc)

@@ -62,6 +62,21 @@ def test_rays_and_hits_golden(G, S, name, which):
     assert np.array_equal(occ, G[f"{name}_occ2"])
 
 
+@pytest.mark.parametrize("post_limit", [-1, 0, 2])
+@pytest.mark.parametrize("name", ["cornell", "terrain"])
+def test_if_if_step_same_hits(G, S, name, post_limit):
+    """trav_step_ii (the step the persistent warps run on real trees) returns exactly what trav_step does: default
+    parking limit, no parking at all (0) and a nearly full stack (2)."""
+    hc = HostCheck(S[name])
+    for sfx in ("", "2"):
+        a = hc.trace(G[f"{name}_org{sfx}"], G[f"{name}_dir{sfx}"])
+        b = hc.trace_ii(G[f"{name}_org{sfx}"], G[f"{name}_dir{sfx}"], post_limit=post_limit)
+        assert a.tobytes() == b.tobytes()
+    a = hc.trace(G[f"{name}_org2"], G[f"{name}_dir2_any"], any_hit=True)
+    b = hc.trace_ii(G[f"{name}_org2"], G[f"{name}_dir2_any"], any_hit=True, post_limit=post_limit)
+    assert np.array_equal(a, b) and np.array_equal(b, G[f"{name}_occ2"])
+
+
 def test_survey_cornell_kats(S):
     # SURVEY.md Appendix D: camera rays with u2 = (0.5, 0.5) on the shipped 1024^2 Cornell scene
     o = Oracle(S["cornell"])
