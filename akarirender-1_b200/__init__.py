@@ -49,11 +49,14 @@ class Backend:
     """A committed scene on the device: the replacement for `scene.accel = BVHAccelerator; scene.commit()` +
     `gpu::Integrator::render` (core/nodes/scene.cpp:119-162)."""
 
-    def __init__(self, scene, device_index=0):
+    def __init__(self, scene, device_index=0, bvh_build=0):
+        """bvh_build: abi.BVH_DEFAULT / BVH_HOST_SAH / BVH_DEVICE_LBVH (include/akari_b200.h akb_bvh_build)."""
         self.lib = init(device_index)
         self.scene = scene
         self.width, self.height = scene.camera.resolution
         desc, keep = scene.flatten()
+        if bvh_build:
+            desc.bvh_build = bvh_build
         h = C.c_void_p()
         _check(self.lib, self.lib.akb_scene_create(C.byref(desc), C.byref(h)))
         self.h = h
@@ -71,7 +74,7 @@ class Backend:
             pass
 
     def info(self):
-        keys = ["n_triangles", "n_bvh_nodes", "bvh_bytes", "n_lights", "triangle_bytes"]
+        keys = ["n_triangles", "n_bvh_nodes", "bvh_bytes", "n_lights", "triangle_bytes", "bvh_depth", "build_us", "bvh_build"]
         return {k: int(self.lib.akb_scene_info(self.h, i)) for i, k in enumerate(keys)}
 
     # ---- Scene::intersect / occlude over host ray batches

@@ -14,6 +14,7 @@ INTEGRATOR_PATH, INTEGRATOR_AO = 0, 1
 SAMPLER_LCG, SAMPLER_PCG = 0, 1
 MODE_WAVEFRONT, MODE_MEGAKERNEL = 0, 1
 SPLIT_TILE, SPLIT_SAMPLE = 0, 1
+BVH_DEFAULT, BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1, 2
 
 
 class Material(C.Structure):
@@ -42,7 +43,7 @@ class Camera(C.Structure):
 class SceneDesc(C.Structure):
     _fields_ = [("abi_version", C.c_uint32), ("n_meshes", C.c_uint32), ("meshes", C.POINTER(Mesh)),
                 ("n_materials", C.c_uint32), ("_pad", C.c_uint32), ("materials", C.POINTER(Material)),
-                ("camera", Camera), ("n_textures", C.c_uint32), ("_pad2", C.c_uint32), ("textures", C.POINTER(Texture))]
+                ("camera", Camera), ("n_textures", C.c_uint32), ("bvh_build", C.c_uint32), ("textures", C.POINTER(Texture))]
 
 
 class RenderParams(C.Structure):

@@ -428,7 +428,12 @@ struct Collapser {
 
 } // namespace
 
+void bvh8_collapse_params(float *node_cost, float *prim_cost, int *max_leaf) {
+    *node_cost = 1.0f, *prim_cost = env_float("AKB_BVH_PRIM_COST", 0.3f), *max_leaf = kMaxLeaf;
+}
+
 void build_bvh8(const float *lo, const float *hi, size_t n, float pad, int n_threads, Bvh8 *out) {
+    out->built_by = 1;
     auto t0 = std::chrono::steady_clock::now();
     out->pad = pad;
     if (n == 0) {

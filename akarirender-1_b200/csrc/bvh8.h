@@ -32,9 +32,14 @@ struct Bvh8 {
     float pad = 0;                   // conservative padding added to every triangle box
     double sah_cost = 0;
     double build_seconds = 0;
+    int built_by = 1; // akb_bvh_build that produced the tree (1 host SAH, 2 device LBVH)
 };
 
 constexpr int kMaxBvh8Depth = 30; // traverse.cuh keeps a 32-entry stack
+
+// Cost-model constants of the 8-wide collapse (node visit, primitive test, triangles per leaf slot), shared with the
+// device builder (bvh_build.cu).
+void bvh8_collapse_params(float *node_cost, float *prim_cost, int *max_leaf);
 
 // lo/hi: n x 3 triangle bounds. Boxes are padded by `pad` on every side before the build.
 void build_bvh8(const float *lo, const float *hi, size_t n, float pad, int n_threads, Bvh8 *out);

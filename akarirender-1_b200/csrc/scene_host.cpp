@@ -65,7 +65,7 @@ inline float i2f(int32_t i) {
 
 } // namespace
 
-akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, std::string *err) {
+akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, std::string *err, BvhBuilder builder) {
     auto fail = [&](const char *msg) {
         if (err) *err = msg;
         return AKB_INVALID_ARG;
@@ -224,7 +224,12 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
     // scene's coordinate magnitude away (error <= |p - o| * 2^-21.6 per plane)
     const float pad = fmaxf(max_abs, 1e-30f) * 3.814697265625e-06f; // 2^-18
     if (n_threads <= 0) n_threads = (int)std::max(1u, std::thread::hardware_concurrency());
-    build_bvh8(blo.data(), bhi.data(), (size_t)nt, pad, n_threads, &hs->bvh);
+    if (builder) {
+        std::string why;
+        if (!builder(blo.data(), bhi.data(), (size_t)nt, pad, n_threads, &hs->bvh, &why)) return fail(("akb_scene_create: " + why).c_str());
+    } else {
+        build_bvh8(blo.data(), bhi.data(), (size_t)nt, pad, n_threads, &hs->bvh);
+    }
     if (hs->bvh.depth > kMaxBvh8Depth) return fail("akb_scene_create: BVH deeper than the traversal stack");
     hs->tris.resize(3 * nt);
     for (uint64_t i = 0; i < nt; i++) {

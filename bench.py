@@ -286,11 +286,11 @@ def main():
             n_launch = max(1, (stp.n_kernel_launches - 2) // 2)
             bytes_total = BYTES_CLOSEST * stp.n_closest_rays + BYTES_ANY * stp.n_shadow_rays
             achieved = bytes_total / (stp.ms_extend * 1e-3) / 1e9 if stp.ms_extend > 0 else None
-            traffic, counters = None, {}
+            traffic, counters, tj = None, {}, {}
             try:
                 with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
                     tj = json.load(f)
-                traffic = 2 * tj["wf_trace_dram_bytes_per_half_frame_launch"]  # the capture is one of two half-frame launches
+                traffic = tj["wf_trace_dram_bytes_per_full_frame_launch"]  # both half-frame launches of one bounce
                 counters = {k[len("wf_trace_"):]: v for k, v in tj.items() if k.startswith("wf_trace_") and k.endswith(("_pct", "_instruction", "_of_peak"))}
             except Exception:
                 pass
@@ -300,7 +300,7 @@ def main():
                     "avg_launch_ms": stp.ms_extend / n_launch, "bytes_per_launch": bytes_total / n_launch,
                     "kernel_share_of_step": stp.ms_extend / stp.ms_total, "shade_share_of_step": stp.ms_shade / stp.ms_total,
                     "mrays_per_s_in_kernel": (stp.n_closest_rays + stp.n_shadow_rays) / (stp.ms_extend * 1e-3) / 1e6,
-                    "ncu_counters": counters, "ncu_source": "profiles/r01f_wf_full.md",
+                    "ncu_counters": counters, "ncu_source": tj.get("source") if traffic else None,
                     "note": "BVH traversal is latency/issue/L2-bound, not HBM-streaming-bound; the HBM fraction is low by "
                             "construction (SURVEY.md §8d): ncu_counters carries the issue-slot / pipe / lane figures of the "
                             "same kernel"}

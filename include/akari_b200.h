@@ -95,6 +95,19 @@ typedef struct akb_camera {
     float focal_distance;
 } akb_camera;
 
+/* Who builds the 8-wide BVH at akb_scene_create (the reference builds its binary SBVH on the host inside
+ * scene.commit(), kernel/bvh-accelerator.h:72-87,671-678). Any choice gives the same hits and films (traverse.h's
+ * result contract does not depend on the tree) except where the reference's triangle test itself is ill-conditioned
+ * (a grazing ray with |a| barely above the 1e-6 reject can "hit" a triangle at a computed point outside the
+ * triangle's box: whether any tree - the reference's own included - reaches that test depends on its boxes; measured
+ * about 2.5e-8 of rays on C3). The choices differ in build time and traversal speed.
+ *   DEFAULT: AKB_BVH_BUILD=host|device in the environment, else HOST_SAH below 4 Mi triangles and DEVICE_LBVH from
+ *            there on (where the host build takes seconds).
+ *   HOST_SAH: binned-SAH binary build on the host threads + optimal 8-wide collapse (csrc/bvh8.cpp).
+ *   DEVICE_LBVH: Morton order + binary radix tree + the same collapse, all on the GPU (csrc/bvh_build.cu);
+ *                falls back to HOST_SAH when the tree would be deeper than the traversal stack. */
+typedef enum akb_bvh_build { AKB_BVH_DEFAULT = 0, AKB_BVH_HOST_SAH = 1, AKB_BVH_DEVICE_LBVH = 2 } akb_bvh_build;
+
 typedef struct akb_scene_desc {
     uint32_t abi_version; /* AKB_ABI_VERSION */
     uint32_t n_meshes;
@@ -104,7 +117,7 @@ typedef struct akb_scene_desc {
     const akb_material *materials;
     akb_camera camera;
     uint32_t n_textures;
-    uint32_t _pad2;
+    uint32_t bvh_build; /* akb_bvh_build; 0 in descriptions written before the field had a meaning */
     const akb_texture *textures;
 } akb_scene_desc;
 
@@ -180,7 +193,7 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene);
 akb_status akb_scene_destroy(akb_scene *scene);
 
 /* Scene facts (for tests/benches): 0 n_triangles, 1 n_bvh_nodes, 2 bvh_bytes, 3 n_lights, 4 triangle_bytes,
- * 5 bvh_depth, 6 build_us. */
+ * 5 bvh_depth, 6 build_us (BVH build wall time), 7 the akb_bvh_build that produced the tree. */
 uint64_t akb_scene_info(const akb_scene *scene, int what);
 
 /* ---- the hot path ------------------------------------------------------------------------------------ */

@@ -7,6 +7,7 @@
 // libakari_b200.so exports none of this: behind the C ABI there is only the CUDA path.
 #define AKB_TRAV_STATS 1
 #include <atomic>
+#include <functional>
 #include <string>
 #include <thread>
 #include <vector>
@@ -192,6 +193,135 @@ int hc_trace_ii(void *hv, const float *org, const float *dir, size_t n, int any_
         }
     }
     return 0;
+}
+// Debug aid: one pixel of the Path integrator (LCG sampler), every ray also traced by brute force over all
+// triangles with the same triangle test and tie rule; prints the rays whose results differ. Returns their number.
+int hc_debug_pixel(void *hv, const akb_render_params *p, int x, int y) {
+    HC *h = (HC *)hv;
+    const SceneDev &S = h->dev;
+    const int W = S.cam.width;
+    const size_t nt = h->hs.n_tris;
+    auto brute = [&](const RaySeg &r, bool any, RayHit &best) {
+        best.tri = -1, best.t = r.tmax;
+        float tb = r.tmax;
+        for (size_t i = 0; i < nt; i++) {
+            const float4 *tp = S.tris + 3 * i;
+            float t, u, v;
+            if (!mt_test(r.o, r.d, r.tmin, any ? r.tmax : INFINITY, tp[0], tp[1], tp[2], t, u, v)) continue;
+            if (any) {
+                best.tri = (int)akb_f2u(tp[0].w), best.t = t, best.u = u, best.v = v;
+                return true;
+            }
+            const int id = (int)akb_f2u(tp[0].w);
+            if (t < tb || (t == tb && best.tri >= 0 && id < best.tri)) tb = t, best.t = t, best.u = u, best.v = v, best.tri = id;
+        }
+        return best.tri >= 0;
+    };
+    int bad = 0;
+    Rng<AKB_SAMPLER_LCG> rng;
+    rng.set_sample_index((uint64_t)(x + y * W));
+    for (int s = 0; s < p->spp; s++) {
+        PathState<AKB_SAMPLER_LCG> ps;
+        ps.L = mk3(0, 0, 0), ps.beta = mk3(1, 1, 1), ps.depth = 0, ps.rng = rng;
+        float u1x, u1y, u2x, u2y;
+        ps.rng.next2d(u2x, u2y);
+        ps.rng.next2d(u1x, u1y);
+        RaySeg ray;
+        camera_generate_ray(S.cam, u2x, u2y, x, y, ray.o, ray.d);
+        ray.tmin = AKB_EPS, ray.tmax = INFINITY;
+        for (;;) {
+            RayHit hit, bh;
+            const bool got = traverse8<false>(S.nodes, S.tris, ray.o, ray.d, ray.tmin, ray.tmax, hit);
+            const bool bgot = brute(ray, false, bh);
+            if (got != bgot || (got && (hit.tri != bh.tri || hit.t != bh.t))) {
+                bad++;
+                fprintf(stderr, "sample %d depth %d closest: tree %d t=%.9g (u %.9g v %.9g)  brute %d t=%.9g (u %.9g v %.9g)\n  o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g) tmin=%.9g\n",
+                        s, ps.depth, got ? hit.tri : -1, hit.t, hit.u, hit.v, bgot ? bh.tri : -1, bh.t, bh.u, bh.v, ray.o.x, ray.o.y, ray.o.z,
+                        ray.d.x, ray.d.y, ray.d.z, ray.tmin);
+            }
+            if (!got) break;
+            RaySeg next, sh;
+            v3 sc;
+            int fl = path_vertex<AKB_SAMPLER_LCG>(S, ps, ray.d, hit.u, hit.v, hit.tri, p->max_depth, p->rr_start_depth, next, sh, sc);
+            if (fl & VTX_SHADOW) {
+                RayHit dummy, bd;
+                const bool occ = traverse8<true>(S.nodes, S.tris, sh.o, sh.d, sh.tmin, sh.tmax, dummy);
+                const bool bocc = brute(sh, true, bd);
+                if (occ != bocc) {
+                    bad++;
+                    fprintf(stderr, "  brute occluder: flat tri %d t=%.9g u=%.9g v=%.9g\n", bd.tri, bd.t, bd.u, bd.v);
+                    fprintf(stderr, "sample %d depth %d shadow: tree %d brute %d\n  o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g) tmin=%.9g tmax=%.9g\n", s, ps.depth,
+                            (int)occ, (int)bocc, sh.o.x, sh.o.y, sh.o.z, sh.d.x, sh.d.y, sh.d.z, sh.tmin, sh.tmax);
+                }
+                if (!occ) ps.L = add3(ps.L, sc);
+            }
+            if (!(fl & VTX_CONTINUE)) break;
+            ray = next;
+        }
+        rng = ps.rng;
+    }
+    return bad;
+}
+// Debug aid: walk from the root to the leaf slot holding flat triangle `flat_tri` and print, per ancestor, the
+// traversal's slab arithmetic for the child on the path next to the exact (double) interval of the dequantised box.
+int hc_debug_path(void *hv, const float *o, const float *d, float tmin, float tmax, int flat_tri) {
+    HC *h = (HC *)hv;
+    const Bvh8 &B = h->hs.bvh;
+    // position of the triangle in leaf order
+    long pos = -1;
+    for (size_t i = 0; i < B.tri_order.size(); i++)
+        if ((int)B.tri_order[i] == flat_tri) pos = (long)i;
+    if (pos < 0) return -1;
+    // find the path by DFS
+    std::vector<std::pair<uint32_t, int>> path; // (node, slot)
+    std::function<bool(uint32_t)> dfs = [&](uint32_t ni) {
+        const Node8 &nd = B.nodes[ni];
+        uint32_t ci = nd.child_base;
+        for (int s = 0; s < 8; s++) {
+            if (nd.meta[s] == 0) continue;
+            if (nd.imask & (1u << s)) {
+                path.push_back({ni, s});
+                if (dfs(ci)) return true;
+                path.pop_back();
+                ci++;
+            } else {
+                const int off = nd.meta[s] & 31, cnt = __builtin_popcount(nd.meta[s] >> 5);
+                if (pos >= (long)nd.tri_base + off && pos < (long)nd.tri_base + off + cnt) {
+                    path.push_back({ni, s});
+                    return true;
+                }
+            }
+        }
+        return false;
+    };
+    if (!dfs(0)) return -2;
+    Trav T;
+    trav_init(T, mk3(o[0], o[1], o[2]), mk3(d[0], d[1], d[2]), tmin, tmax, true);
+    const float idv[3] = {T.idx, T.idy, T.idz}, ov[3] = {o[0], o[1], o[2]};
+    for (auto &ps : path) {
+        const Node8 &nd = B.nodes[ps.first];
+        const int s = ps.second;
+        const uint8_t *ql[3] = {nd.qlox, nd.qloy, nd.qloz}, *qh[3] = {nd.qhix, nd.qhiy, nd.qhiz};
+        float cmin = tmin, cmax = tmax;
+        double emin = tmin, emax = tmax;
+        fprintf(stderr, "node %u slot %d meta %02x:\n", ps.first, s, nd.meta[s]);
+        for (int a = 0; a < 3; a++) {
+            const float adj = akb_u2f((uint32_t)nd.e[a] << 23) * idv[a];
+            const float org = fmaf(-32768.0f, adj, (nd.p[a] - ov[a]) * idv[a]);
+            const uint8_t qn = idv[a] < 0 ? qh[a][s] : ql[a][s], qf = idv[a] < 0 ? ql[a][s] : qh[a][s];
+            const float tl = fmaf(32768.0f + (float)qn, adj, org), th = fmaf(32768.0f + (float)qf, adj, org);
+            const double sc = ldexp(1.0, (int)nd.e[a] - 127);
+            const double blo = (double)nd.p[a] + ql[a][s] * sc, bhi = (double)nd.p[a] + qh[a][s] * sc;
+            const double e0 = (blo - (double)ov[a]) / (double)d[a], e1 = (bhi - (double)ov[a]) / (double)d[a];
+            fprintf(stderr, "   axis %d: box [%.9g, %.9g] q [%d,%d]  traversal tl %.9g th %.9g   exact %.12g %.12g\n", a, blo, bhi, ql[a][s], qh[a][s], tl, th,
+                    std::min(e0, e1), std::max(e0, e1));
+            cmin = fmaxf(cmin, tl), cmax = fminf(cmax, th);
+            emin = std::max(emin, std::min(e0, e1)), emax = std::min(emax, std::max(e0, e1));
+        }
+        fprintf(stderr, "   traversal [%.9g, %.9g] %s   exact [%.12g, %.12g] %s\n", cmin, cmax, cmin <= cmax ? "HIT" : "MISS", emin, emax,
+                emin <= emax ? "hit" : "miss");
+    }
+    return (int)path.size();
 }
 int hc_generate_rays(void *hv, const int32_t *xy, const float *u2, size_t n, float *org, float *dir) {
     const SceneDev &S = ((HC *)hv)->dev;

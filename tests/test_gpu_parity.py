@@ -121,6 +121,44 @@ def test_both_traversal_steps_bit_identical(G, S, name):
     assert np.array_equal(np.frombuffer(out[0][1], np.int32), G[f"{name}_occ2"])
 
 
+def test_device_bvh_build_same_results(G, S):
+    """akb_bvh_build DEVICE_LBVH (csrc/bvh_build.cu) builds another tree; the traversal's result contract does not
+    depend on the tree, so hits, occlusion and films must match the golden vectors / the host-built tree bit for bit."""
+    for name in ("cornell", "terrain"):
+        sc = S[name]
+        be = pkg.Backend(sc, 0, bvh_build=abi.BVH_DEVICE_LBVH)
+        info = be.info()
+        assert info["bvh_build"] == abi.BVH_DEVICE_LBVH and 1 <= info["bvh_depth"] <= 30, info
+        for sfx in ("", "2"):
+            h = be.trace(G[f"{name}_org{sfx}"], G[f"{name}_dir{sfx}"])
+            bad, ties, tb = hit_mismatch(G[f"{name}_hits{sfx}"], h)
+            assert bad == 0 and tb == 0, (name, sfx, bad, ties, tb)
+        occ = be.trace(G[f"{name}_org2"], G[f"{name}_dir2_any"], any_hit=True)
+        assert np.array_equal(occ, G[f"{name}_occ2"])
+        ref = backend(sc)
+        assert ref.info()["bvh_build"] == abi.BVH_HOST_SAH
+        assert same_bits(be.render()[0], ref.render()[0])
+        be.close(), ref.close()
+    # scenes with 1, 2, 3 and 5 triangles, coincident centroids, and a NaN vertex
+    rng = np.random.default_rng(5)
+    for nt in (1, 2, 3, 5, 64):
+        v = rng.uniform(-1, 1, (nt, 3, 3)).astype(np.float32)
+        if nt == 64:
+            v[:] = v[0]  # 64 copies of one triangle: all Morton keys equal
+        if nt == 5:
+            v[3, 1, 2] = np.nan
+        mesh = scenes.AkariMesh(materials=[scenes.DiffuseMaterial(0.5)], vertices=v.reshape(-1, 3),
+                                indices=np.arange(3 * nt, dtype=np.int32), material_indices=np.zeros(nt, np.int32))
+        sc = scenes.Scene(scenes.PerspectiveCamera(fov=60, resolution=(16, 16)), scenes.Path(spp=1, ray_clamp=0.0), [mesh])
+        org, dr = random_rays(rng, 20000, (-2, -2, -2), (2, 2, 2))
+        a, b = pkg.Backend(sc, 0, bvh_build=abi.BVH_DEVICE_LBVH), backend(sc)
+        assert a.info()["bvh_build"] == abi.BVH_DEVICE_LBVH
+        ha, hb = a.trace(org, dr), b.trace(org, dr)
+        assert ha.tobytes() == hb.tobytes(), nt
+        assert (ha["prim_id"] >= 0).sum() > 0
+        a.close(), b.close()
+
+
 def test_wavefront_equals_megakernel_and_sorting_is_neutral():
     sc = scenes.mixed_box((80, 56), 6, 5)
     be = backend(sc)
