@@ -257,8 +257,10 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
             build = nt >= (4u << 20) ? AKB_BVH_DEVICE_LBVH : AKB_BVH_HOST_SAH;
     }
     if (build != AKB_BVH_HOST_SAH && build != AKB_BVH_DEVICE_LBVH) return set_err(AKB_INVALID_ARG, "akb_scene_create: bad bvh_build %d", build);
+    const auto t_create = std::chrono::steady_clock::now();
     st = flatten_scene(desc, 0, &hs, &err, build == AKB_BVH_DEVICE_LBVH ? device_bvh_builder : nullptr);
     if (st != AKB_OK) return set_err(st, "%s", err.c_str());
+    const auto t_flat = std::chrono::steady_clock::now();
     akb_scene *sc = new akb_scene();
     SceneDev &S = sc->dev;
     memset(&S, 0, sizeof S);
@@ -297,6 +299,11 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
     if (st != AKB_OK) {
         delete sc;
         return st;
+    }
+    if (getenv("AKB_BVH_VERBOSE")) {
+        const auto t_up = std::chrono::steady_clock::now();
+        fprintf(stderr, "[akb] scene create: flatten + BVH %.3f s (BVH %.3f s), upload %.3f s\n", std::chrono::duration<double>(t_flat - t_create).count(),
+                hs.bvh.build_seconds, std::chrono::duration<double>(t_up - t_flat).count());
     }
     S.light_func_int = hs.light_func_int;
     S.n_lights = (int)hs.light_func.size();

@@ -6,6 +6,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <thread>
 
 namespace akb {
@@ -70,6 +72,7 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
         if (err) *err = msg;
         return AKB_INVALID_ARG;
     };
+    const auto t_f0 = std::chrono::steady_clock::now();
     if (!d) return fail("akb_scene_create: null description");
     if (d->abi_version != AKB_ABI_VERSION) return fail("akb_scene_create: abi_version mismatch");
     if (d->n_meshes && !d->meshes) return fail("akb_scene_create: meshes == NULL");
@@ -129,9 +132,30 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
         float uv[3][2];
     };
     std::vector<LightSrc> light_src;
-    for (uint32_t g = 0; g < d->n_meshes; g++) {
+    if (n_threads <= 0) n_threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    // per-triangle records, in chunks of one mesh's triangles over the host threads; emissive triangles are collected
+    // per chunk and concatenated in (mesh, prim) order, which is the reference's light order
+    struct Chunk {
+        uint32_t g;
+        uint64_t p0, p1;
+        float max_abs = 0;
+        const char *error = nullptr;
+        std::vector<LightSrc> lights;
+    };
+    std::vector<Chunk> chunks;
+    for (uint32_t g = 0; g < d->n_meshes; g++)
+        for (uint64_t p0 = 0; p0 < d->meshes[g].n_triangles; p0 += 65536) {
+            Chunk c;
+            c.g = g, c.p0 = p0, c.p1 = std::min<uint64_t>(p0 + 65536, d->meshes[g].n_triangles);
+            chunks.push_back(std::move(c));
+        }
+    auto do_chunk = [&](Chunk &ck) {
+        auto fail = [&](const char *msg) { ck.error = msg; }; // shadows the outer one: a worker records, the caller reports
+        float max_abs = 0;
+        std::vector<LightSrc> &light_src = ck.lights;
+        const uint32_t g = ck.g;
         const akb_mesh &m = d->meshes[g];
-        for (uint64_t p = 0; p < m.n_triangles; p++) {
+        for (uint64_t p = ck.p0; p < ck.p1; p++) {
             const uint64_t t = hs->geom_offset[g] + p;
             v3 v[3], n[3];
             for (int i = 0; i < 3; i++) { // get_triangle, kernel/instance.h:83-97
@@ -172,6 +196,22 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
                 light_src.push_back(ls);
             }
         }
+        ck.max_abs = max_abs;
+    };
+    {
+        std::atomic<size_t> next{0};
+        auto work = [&]() {
+            for (size_t i; (i = next.fetch_add(1)) < chunks.size();) do_chunk(chunks[i]);
+        };
+        std::vector<std::thread> th;
+        for (int i = 1; i < std::min<int>(n_threads, (int)chunks.size()); i++) th.emplace_back(work);
+        work();
+        for (auto &t : th) t.join();
+    }
+    for (Chunk &ck : chunks) {
+        if (ck.error) return fail(ck.error);
+        max_abs = fmaxf(max_abs, ck.max_abs);
+        light_src.insert(light_src.end(), ck.lights.begin(), ck.lights.end());
     }
     // area lights in (mesh, prim) order + power distribution, core/nodes/scene.cpp:58-92
     const size_t nl = light_src.size();
@@ -223,7 +263,7 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
     // conservative box padding: covers the rounding of the quantised slab test for ray origins up to ~12x the
     // scene's coordinate magnitude away (error <= |p - o| * 2^-21.6 per plane)
     const float pad = fmaxf(max_abs, 1e-30f) * 3.814697265625e-06f; // 2^-18
-    if (n_threads <= 0) n_threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    const auto t_b0 = std::chrono::steady_clock::now();
     if (builder) {
         std::string why;
         if (!builder(blo.data(), bhi.data(), (size_t)nt, pad, n_threads, &hs->bvh, &why)) return fail(("akb_scene_create: " + why).c_str());
@@ -231,12 +271,29 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
         build_bvh8(blo.data(), bhi.data(), (size_t)nt, pad, n_threads, &hs->bvh);
     }
     if (hs->bvh.depth > kMaxBvh8Depth) return fail("akb_scene_create: BVH deeper than the traversal stack");
+    const auto t_b1 = std::chrono::steady_clock::now();
     hs->tris.resize(3 * nt);
-    for (uint64_t i = 0; i < nt; i++) {
-        uint32_t t = hs->bvh.tri_order[i];
-        hs->tris[3 * i] = leaf_rec[3 * (size_t)t];
-        hs->tris[3 * i + 1] = leaf_rec[3 * (size_t)t + 1];
-        hs->tris[3 * i + 2] = leaf_rec[3 * (size_t)t + 2];
+    {
+        const uint64_t step = 1 << 16;
+        std::atomic<uint64_t> next{0};
+        auto work = [&]() {
+            for (uint64_t b; (b = next.fetch_add(step)) < nt;)
+                for (uint64_t i = b; i < std::min(nt, b + step); i++) {
+                    const uint32_t t = hs->bvh.tri_order[i];
+                    hs->tris[3 * i] = leaf_rec[3 * (size_t)t];
+                    hs->tris[3 * i + 1] = leaf_rec[3 * (size_t)t + 1];
+                    hs->tris[3 * i + 2] = leaf_rec[3 * (size_t)t + 2];
+                }
+        };
+        std::vector<std::thread> th;
+        for (int i = 1; i < std::min<uint64_t>((uint64_t)n_threads, (nt + step - 1) / step); i++) th.emplace_back(work);
+        work();
+        for (auto &t : th) t.join();
+    }
+    if (getenv("AKB_BVH_VERBOSE")) {
+        const auto t_b2 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[akb] flatten: records %.3f s, BVH %.3f s, leaf order %.3f s\n", std::chrono::duration<double>(t_b0 - t_f0).count(),
+                std::chrono::duration<double>(t_b1 - t_b0).count(), std::chrono::duration<double>(t_b2 - t_b1).count());
     }
     return AKB_OK;
 }
