@@ -28,7 +28,7 @@ static double now_s() {
 
 int main(int argc, char **argv) {
     const char *input = nullptr, *pfm = nullptr, *output = nullptr;
-    int device = 0, spp = -1, max_depth = -1;
+    int device = 0, spp = -1, max_depth = -1, bvh = AKB_BVH_DEFAULT;
     for (int i = 1; i < argc; i++) {
         const std::string a = argv[i];
         auto next = [&]() -> const char * {
@@ -43,13 +43,17 @@ int main(int argc, char **argv) {
         else if (a == "--spp") spp = atoi(next());
         else if (a == "--max-depth") max_depth = atoi(next());
         else if (a == "--pfm") pfm = next();
+        else if (a == "--bvh") {
+            const std::string v = next();
+            bvh = v == "host" ? AKB_BVH_HOST_SAH : (v == "device" ? AKB_BVH_DEVICE_LBVH : AKB_BVH_DEFAULT);
+        }
         else if (a == "-o" || a == "--output") output = next();
         else if (a == "-i" || a == "--input") input = next();
         else if (a == "-h" || a == "--help") input = nullptr, i = argc;
         else input = argv[i];
     }
     if (!input) {
-        printf("usage: akari-b200 [--gpu] [-d device] [--spp N] [--max-depth N] [-o out.png] [--pfm out.pfm] scene.akari\n");
+        printf("usage: akari-b200 [--gpu] [-d device] [--spp N] [--max-depth N] [--bvh host|device] [-o out.png] [--pfm out.pfm] scene.akari\n");
         return 0;
     }
     CHECK(akb_init(device));
@@ -59,14 +63,17 @@ int main(int argc, char **argv) {
     CHECK(akb_scene_file_params(file, &params));
     if (spp >= 0) params.spp = spp;
     if (max_depth >= 0) params.max_depth = max_depth;
-    const akb_scene_desc *desc = akb_scene_file_desc(file);
+    akb_scene_desc desc_copy = *akb_scene_file_desc(file);
+    desc_copy.bvh_build = (uint32_t)bvh;
+    const akb_scene_desc *desc = &desc_copy;
     const int W = desc->camera.width, H = desc->camera.height;
     printf("preparing scene\n");
     double t = now_s();
     akb_scene *scene = nullptr;
     CHECK(akb_scene_create(desc, &scene));
-    printf("building acceleration structure took (%.3fs): %llu triangles, %llu BVH8 nodes, %llu lights\n", now_s() - t,
+    printf("building acceleration structure took (%.3fs): %llu triangles, %llu BVH8 nodes (%s build, %.3fs), %llu lights\n", now_s() - t,
            (unsigned long long)akb_scene_info(scene, 0), (unsigned long long)akb_scene_info(scene, 1),
+           akb_scene_info(scene, 7) == AKB_BVH_DEVICE_LBVH ? "device" : "host", akb_scene_info(scene, 6) * 1e-6,
            (unsigned long long)akb_scene_info(scene, 3));
     std::vector<float> film((size_t)W * H * 4);
     akb_render_stats st;

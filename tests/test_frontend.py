@@ -267,4 +267,8 @@ def test_scene_file_renders_like_the_direct_route(tmp_path):
     raw = open(tmp_path / "out.pfm", "rb").read()
     px = np.frombuffer(raw[len(b"PF\n64 48\n-1.0\n"):], "<f4").reshape(48, 64, 3)[::-1]
     assert np.array_equal(px, (fb[..., :3] / fb[..., 3:]).astype(np.float32))
+    # --bvh device: the tree is built on the GPU, the image is the same
+    r = subprocess.run([CLI, path, "--bvh", "device", "-o", "dev.png"], capture_output=True, text=True, cwd=str(tmp_path))
+    assert r.returncode == 0 and "device build" in r.stdout, r.stdout + r.stderr
+    assert np.array_equal(decode_png(str(tmp_path / "dev.png")), b.film_to_srgb8(fb))
     a.close(), b.close()
