@@ -78,12 +78,14 @@ class Backend:
         return {k: int(self.lib.akb_scene_info(self.h, i)) for i, k in enumerate(keys)}
 
     # ---- Scene::intersect / occlude over host ray batches
-    def trace(self, org_tmin, dir_tmax, any_hit=False):
+    def trace(self, org_tmin, dir_tmax, any_hit=False, out=None):
+        """`out`: a caller-owned result array (HIT_DTYPE, or int32 for any_hit) to fill instead of a new one."""
         org = np.ascontiguousarray(org_tmin, np.float32)
         dr = np.ascontiguousarray(dir_tmax, np.float32)
         n = org.shape[0]
-        hits = np.zeros(n, HIT_DTYPE)
-        occ = np.zeros(n, np.int32)
+        hits = out if (out is not None and not any_hit) else np.zeros(0 if any_hit else n, HIT_DTYPE)
+        occ = out if (out is not None and any_hit) else np.zeros(n if any_hit else 0, np.int32)
+        assert (occ if any_hit else hits).shape[0] == n
         _check(self.lib, self.lib.akb_trace(self.h, _ptr(org), _ptr(dr), n, int(any_hit), _ptr(hits), _ptr(occ)))
         return occ if any_hit else hits
 

@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <chrono>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "bvh_build.cuh"
@@ -23,6 +24,7 @@ int g_device = -1;
 int g_n_sms = 0;
 constexpr size_t kMaxBatch = (size_t)1 << 30;
 bool g_profile_stages = false;
+size_t g_trace_chunk = (size_t)1 << 21; // AKB_TRACE_CHUNK: rays per staging slot of akb_trace (host batches)
 int g_pipelines = 2;                   // AKB_PIPELINES: half-frame pipelines of the wavefront (1 or 2)
 int g_pipeline_min_slots = 128 * 1024; // AKB_PIPELINE_MIN_SLOTS: below this one pipeline keeps the launches large
 
@@ -68,7 +70,30 @@ struct akb_scene {
     float4 *d_film = nullptr;
     size_t d_film_px = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // akb_trace (host ray batches): two staging slots of pinned host + device buffers, each on its own stream, so that
+    // the host-side copies, both PCIe directions and the traversal kernel of consecutive chunks overlap
+    struct TraceSlot {
+        char *h_in = nullptr, *h_out = nullptr; // pinned: org | dir, results
+        float4 *d_o = nullptr, *d_d = nullptr;
+        void *d_out = nullptr;
+        uint32_t *cursor = nullptr;
+        cudaStream_t st = nullptr;
+    } trace_slot[2];
+    size_t trace_cap = 0; // rays per slot
 
+    void free_trace() {
+        for (TraceSlot &t : trace_slot) {
+            if (t.h_in) cudaFreeHost(t.h_in);
+            if (t.h_out) cudaFreeHost(t.h_out);
+            if (t.d_o) cudaFree(t.d_o);
+            if (t.d_d) cudaFree(t.d_d);
+            if (t.d_out) cudaFree(t.d_out);
+            if (t.cursor) cudaFree(t.cursor);
+            if (t.st) cudaStreamDestroy(t.st);
+            t = TraceSlot();
+        }
+        trace_cap = 0;
+    }
     void free_ws() {
         for (void *p : ws_allocs) cudaFree(p);
         ws_allocs.clear();
@@ -76,6 +101,7 @@ struct akb_scene {
     }
     ~akb_scene() {
         free_ws();
+        free_trace();
         for (void *p : allocs) cudaFree(p);
         if (d_ctr) cudaFree(d_ctr);
         if (h_ctr) cudaFreeHost(h_ctr);
@@ -89,6 +115,25 @@ struct akb_scene {
 };
 
 namespace {
+
+// memcpy over a few host threads: one core moves ~10 GB/s, less than one direction of the PCIe link
+void host_copy(void *dst, const void *src, size_t bytes) {
+    const size_t piece = (size_t)4 << 20;
+    const int n_threads = (int)std::min<size_t>(8, bytes / piece);
+    if (n_threads <= 1) {
+        memcpy(dst, src, bytes);
+        return;
+    }
+    std::vector<std::thread> th;
+    const size_t per = ((bytes / n_threads) + 4095) & ~(size_t)4095;
+    for (int i = 0; i < n_threads; i++) {
+        const size_t b = (size_t)i * per, e = std::min(bytes, b + per);
+        if (b >= e) break;
+        th.emplace_back([=]() { memcpy((char *)dst + b, (const char *)src + b, e - b); });
+    }
+    for (auto &t : th) t.join();
+}
+
 
 template <class T> akb_status upload(akb_scene *sc, const T *src, size_t n, const T **dst) {
     void *p = nullptr;
@@ -187,6 +232,7 @@ akb_status akb_init(int device_index) {
     const char *pf = getenv("AKB_PROFILE_STAGES");
     g_profile_stages = pf && pf[0] == '1';
     if (const char *e = getenv("AKB_PIPELINES")) g_pipelines = atoi(e);
+    if (const char *e = getenv("AKB_TRACE_CHUNK")) g_trace_chunk = std::max<size_t>(1024, (size_t)atoll(e));
     if (const char *e = getenv("AKB_PIPELINE_MIN_SLOTS")) g_pipeline_min_slots = atoi(e);
     if (const char *rb = getenv("AKB_REFILL_BELOW")) {
         int v = atoi(rb);
@@ -516,25 +562,51 @@ akb_status akb_trace(akb_scene *sc, const float *org, const float *dir, size_t n
     if (st != AKB_OK) return st;
     if (!sc || (n && (!org || !dir)) || (n && !any_hit && !out_hits) || (n && any_hit && !out_occ))
         return set_err(AKB_INVALID_ARG, "akb_trace: null argument");
-    const size_t chunk = std::min<size_t>(n, (size_t)1 << 24);
     if (n == 0) return AKB_OK;
-    float4 *d_o = nullptr, *d_d = nullptr;
-    void *d_out = nullptr;
     const size_t out_elt = any_hit ? sizeof(int32_t) : sizeof(akb_hit);
-    cudaError_t e = cudaMalloc((void **)&d_o, chunk * sizeof(float4));
-    if (e == cudaSuccess) e = cudaMalloc((void **)&d_d, chunk * sizeof(float4));
-    if (e == cudaSuccess) e = cudaMalloc(&d_out, chunk * out_elt);
-    for (size_t off = 0; off < n && e == cudaSuccess; off += chunk) {
-        const size_t m = std::min(chunk, n - off);
-        e = cudaMemcpy(d_o, org + 4 * off, m * sizeof(float4), cudaMemcpyHostToDevice);
-        if (e == cudaSuccess) e = cudaMemcpy(d_d, dir + 4 * off, m * sizeof(float4), cudaMemcpyHostToDevice);
-        if (e == cudaSuccess) e = launch_trace_batch(sc->dev, d_o, d_d, m, any_hit, (akb_hit *)d_out, (int32_t *)d_out, &sc->d_ctr->fetch_trace, g_n_sms, 0);
-        if (e == cudaSuccess)
-            e = cudaMemcpy(any_hit ? (void *)(out_occ + off) : (void *)(out_hits + off), d_out, m * out_elt, cudaMemcpyDeviceToHost);
+    const size_t chunk = std::min<size_t>(n, g_trace_chunk);
+    cudaError_t e = cudaSuccess;
+    if (sc->trace_cap < chunk) { // (re)size the staging slots; kept with the scene: pinning memory is slow
+        sc->free_trace();
+        for (akb_scene::TraceSlot &t : sc->trace_slot) {
+            if (e == cudaSuccess) e = cudaMallocHost((void **)&t.h_in, chunk * 2 * sizeof(float4));
+            if (e == cudaSuccess) e = cudaMallocHost((void **)&t.h_out, chunk * sizeof(akb_hit));
+            if (e == cudaSuccess) e = cudaMalloc((void **)&t.d_o, chunk * sizeof(float4));
+            if (e == cudaSuccess) e = cudaMalloc((void **)&t.d_d, chunk * sizeof(float4));
+            if (e == cudaSuccess) e = cudaMalloc(&t.d_out, chunk * sizeof(akb_hit));
+            if (e == cudaSuccess) e = cudaMalloc((void **)&t.cursor, sizeof(uint32_t));
+            if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&t.st, cudaStreamNonBlocking);
+        }
+        if (e == cudaSuccess) sc->trace_cap = chunk;
     }
-    cudaFree(d_o), cudaFree(d_d), cudaFree(d_out);
-    if (e != cudaSuccess)
+    char *out = any_hit ? (char *)out_occ : (char *)out_hits;
+    const size_t n_chunks = (n + chunk - 1) / chunk;
+    auto drain = [&](size_t k) { // chunk k's results: wait for its slot, then pinned -> caller
+        akb_scene::TraceSlot &t = sc->trace_slot[k & 1];
+        cudaError_t r = cudaStreamSynchronize(t.st);
+        if (r != cudaSuccess) return r;
+        const size_t off = k * chunk, m = std::min(chunk, n - off);
+        host_copy(out + off * out_elt, t.h_out, m * out_elt);
+        return cudaSuccess;
+    };
+    for (size_t k = 0; k < n_chunks && e == cudaSuccess; k++) {
+        akb_scene::TraceSlot &t = sc->trace_slot[k & 1];
+        if (k >= 2) e = drain(k - 2);
+        if (e != cudaSuccess) break;
+        const size_t off = k * chunk, m = std::min(chunk, n - off);
+        host_copy(t.h_in, org + 4 * off, m * sizeof(float4));
+        host_copy(t.h_in + chunk * sizeof(float4), dir + 4 * off, m * sizeof(float4));
+        e = cudaMemcpyAsync(t.d_o, t.h_in, m * sizeof(float4), cudaMemcpyHostToDevice, t.st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(t.d_d, t.h_in + chunk * sizeof(float4), m * sizeof(float4), cudaMemcpyHostToDevice, t.st);
+        if (e == cudaSuccess) e = launch_trace_batch(sc->dev, t.d_o, t.d_d, m, any_hit, (akb_hit *)t.d_out, (int32_t *)t.d_out, t.cursor, g_n_sms, t.st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(t.h_out, t.d_out, m * out_elt, cudaMemcpyDeviceToHost, t.st);
+    }
+    for (size_t k = n_chunks >= 2 ? n_chunks - 2 : 0; k < n_chunks && e == cudaSuccess; k++) e = drain(k);
+    if (e != cudaSuccess) {
+        cudaStreamSynchronize(sc->trace_slot[0].st), cudaStreamSynchronize(sc->trace_slot[1].st);
+        if (e == cudaErrorMemoryAllocation) sc->free_trace();
         return set_err(e == cudaErrorMemoryAllocation ? AKB_OOM : AKB_CUDA_ERROR, "akb_trace: %s", cudaGetErrorString(e));
+    }
     return AKB_OK;
 }
 

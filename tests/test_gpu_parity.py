@@ -75,6 +75,31 @@ def test_trace_vs_oracle_seeded():
     be.close()
 
 
+def test_host_batches_are_staged_in_chunks():
+    """akb_trace stages host rays through two pinned slots of 2 Mi rays (api.cu): a batch spanning several chunks with
+    a ragged tail must equal the device-resident route (akb_trace_device), closest and any hit."""
+    import torch
+    rng = np.random.default_rng(23)
+    sc = scenes.terrain_scene(n=96, resolution=(64, 36), spp=1)
+    be = backend(sc)
+    n = 2 * (1 << 21) + 12345
+    org, dr = random_rays(rng, n, (-50, -2, -50), (50, 15, 50))
+    d_org, d_dir = torch.from_numpy(org).cuda(), torch.from_numpy(dr).cuda()
+    d_hits = torch.zeros(n * 5, dtype=torch.int32, device="cuda")
+    d_occ = torch.zeros(n, dtype=torch.int32, device="cuda")
+    be.trace_device(d_org.data_ptr(), d_dir.data_ptr(), n, 0, d_hits.data_ptr(), d_occ.data_ptr())
+    h = be.trace(org, dr)
+    assert h.tobytes() == d_hits.cpu().numpy().tobytes()
+    assert (h["prim_id"] >= 0).sum() > n // 10
+    dra = dr.copy()
+    dra[:, 3] = 30.0
+    d_dir.copy_(torch.from_numpy(dra))
+    be.trace_device(d_org.data_ptr(), d_dir.data_ptr(), n, 1, d_hits.data_ptr(), d_occ.data_ptr())
+    assert np.array_equal(be.trace(org, dra, any_hit=True), d_occ.cpu().numpy())
+    assert len(be.trace(org[:0], dr[:0])) == 0 and len(be.trace(org[:7], dr[:7])) == 7
+    be.close()
+
+
 @pytest.mark.parametrize("mode", ["wavefront", "megakernel"])
 def test_films_golden(G, S, mode):
     """Bit-level per-pixel comparison with the reference's float film at equal seeds."""
