@@ -414,13 +414,15 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
     rc.sort_materials = p->sort_materials, rc.ray_clamp = p->ray_clamp;
     rc.seed_offset = shard.seed_offset;
     rc.map = shard.map;
+    rc.ao = p->integrator == AKB_INTEGRATOR_AO, rc.ao_occlude = p->ao_occlude;
+    if (rc.ao) rc.sort_materials = 0, rc.ray_clamp = 0.0f; // AO: no materials, samples are exact 0/1
     const size_t n_px = (size_t)sc->width * sc->height;
     uint64_t launches = 0;
     std::vector<cudaEvent_t> evs;
     CU(cudaMemsetAsync(d_out_rgbw, 0, n_px * sizeof(float4), stream));
     CU(cudaMemsetAsync(sc->d_ctr, 0, 2 * sizeof(Counters), stream));
     CU(cudaEventRecord(sc->ev0, stream));
-    if (p->integrator == AKB_INTEGRATOR_AO) {
+    if (p->integrator == AKB_INTEGRATOR_AO && p->mode == AKB_MODE_MEGAKERNEL) {
         CU(launch_ao(sc->dev, rc, p->ao_occlude, (float4 *)d_out_rgbw, sc->d_ctr, stream));
         launches = 1;
     } else if (p->mode == AKB_MODE_MEGAKERNEL) {

@@ -410,7 +410,10 @@ __global__ void __launch_bounds__(kBlock) wf_trace_kernel(SceneDev S, RenderConf
     }
 }
 
-template <int SAMP, bool TEX>
+// AO = true: the AO integrator on the same queues (kernel/integrators/cpu/integrator.cpp:72-80): a hit vertex emits one
+// cosine-weighted any-hit ray carrying (1,1,1) and the path parks for one step, so that the sample is 1 iff that ray
+// is unoccluded; a miss finishes with 0. Sampler order and film sums are those of ao_kernel.
+template <int SAMP, bool TEX, bool AO>
 __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
     Counters *ctr = ws.ctr;
     // Work list: with material sorting the kNumKeys keyed queues, each padded to a warp so that warps are
@@ -446,7 +449,18 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
             ps.rng.s = ws.rng[slot];
             ps.L = mk3(0, 0, 0); // running L stays in HBM; path_vertex only ever adds emission, at depth 0
             bool finished = true; // path ends at this vertex
-            if (tri >= 0) {
+            if (AO) {
+                if (tri >= 0) {
+                    const RaySeg sh = ao_ray<SAMP>(S, ps.rng, hrec.x, hrec.y, tri, rc.ao_occlude);
+                    ws.sh_o[slot] = mk4(sh.o, sh.tmin);
+                    ws.sh_d[slot] = mk4(sh.d, sh.tmax);
+                    ws.sh_c[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+                    ws.rng[slot] = ps.rng.s;
+                    ext_entry = slot | kDeadRay;
+                    push_sh = push_ext = true, finished = false;
+                    n_parked++;
+                }
+            } else if (tri >= 0) {
                 const float4 bd = ws.beta[slot];
                 const float4 rd = ws.ray_d[slot];
                 ps.beta = xyz(bd), ps.depth = __float_as_int(bd.w);
@@ -457,7 +471,7 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
                 const bool shadow = (fl & VTX_SHADOW) != 0;
                 // A ray leaving a vertex at depth == max_depth can never contribute (kernel/pathtracer.h:102-112: no
                 // emission at depth > 0, no scattering at depth >= max_depth): it is not traced.
-                if (cont && ps.depth >= rc.max_depth && ps.depth > 0) cont = false, n_parked++;
+                if (cont && ps.depth >= rc.max_depth && ps.depth > 0) cont = false;
                 if (shadow) {
                     ws.sh_o[slot] = mk4(sh.o, sh.tmin);
                     ws.sh_d[slot] = mk4(sh.d, sh.tmax);
@@ -475,6 +489,7 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
                     ws.rng[slot] = ps.rng.s;
                     ext_entry = slot | kDeadRay;
                     push_ext = true, finished = false;
+                    n_parked++; // the queue entry is counted by the next traversal launch but traces nothing
                 }
             }
             if (finished) { // "Splat" + regenerate (gpu/cuda/integrator.cpp:385-401, core/film.h:66-70)
@@ -602,19 +617,26 @@ cudaError_t launch_wf_trace(const SceneDev &S, const RenderConfig &rc, const Wor
 
 cudaError_t launch_wf_shade(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int parity, int n_sms,
                             cudaStream_t st) {
-    // four instantiations: sampler x (scene has image textures)
-    static int occ[2][2] = {{blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_LCG, false>, kBlock), blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_LCG, true>, kBlock)},
-                            {blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_PCG, false>, kBlock), blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_PCG, true>, kBlock)}};
+    // six instantiations: sampler x (scene has image textures), and the AO integrator per sampler
+    static int occ[2][3] = {{blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_LCG, false, false>, kBlock), blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_LCG, true, false>, kBlock),
+                             blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_LCG, false, true>, kBlock)},
+                            {blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_PCG, false, false>, kBlock), blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_PCG, true, false>, kBlock),
+                             blocks_per_sm(wf_shade_kernel<AKB_SAMPLER_PCG, false, true>, kBlock)}};
     const bool pcg = rc.sampler == AKB_SAMPLER_PCG, tex = S.n_textures > 0;
-    const int grid = n_sms * occ[pcg][tex];
-    if (pcg && tex)
-        wf_shade_kernel<AKB_SAMPLER_PCG, true><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+    const int which = rc.ao ? 2 : (tex ? 1 : 0);
+    const int grid = n_sms * occ[pcg][which];
+    if (pcg && which == 2)
+        wf_shade_kernel<AKB_SAMPLER_PCG, false, true><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+    else if (which == 2)
+        wf_shade_kernel<AKB_SAMPLER_LCG, false, true><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+    else if (pcg && tex)
+        wf_shade_kernel<AKB_SAMPLER_PCG, true, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
     else if (pcg)
-        wf_shade_kernel<AKB_SAMPLER_PCG, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+        wf_shade_kernel<AKB_SAMPLER_PCG, false, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
     else if (tex)
-        wf_shade_kernel<AKB_SAMPLER_LCG, true><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+        wf_shade_kernel<AKB_SAMPLER_LCG, true, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
     else
-        wf_shade_kernel<AKB_SAMPLER_LCG, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+        wf_shade_kernel<AKB_SAMPLER_LCG, false, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
     return cudaGetLastError();
 }
 

@@ -36,6 +36,8 @@ struct Workspace {
 
 struct RenderConfig {
     int spp, max_depth, rr_start, sampler, sort_materials;
+    int ao;            // AKB_INTEGRATOR_AO on the wavefront queues
+    float ao_occlude;
     float ray_clamp;
     unsigned long long seed_offset; // added to the per-pixel sampler seed x + y*W (AKB_SPLIT_SAMPLE)
     SlotMap map;
