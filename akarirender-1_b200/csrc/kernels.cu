@@ -23,6 +23,9 @@ namespace akb {
 namespace {
 
 constexpr int kBlock = 128;
+#ifndef AKB_TRACE_MIN_BLOCKS
+#define AKB_TRACE_MIN_BLOCKS 8 // traversal kernels: 64 registers, no spills; measured 4 / 6 / 8 / 10 blocks: 29.3 / 23.6 / 22.2 / 24.7 ms
+#endif
 #ifndef AKB_SHADE_MIN_BLOCKS
 #define AKB_SHADE_MIN_BLOCKS 6
 #endif
@@ -150,7 +153,7 @@ struct BatchSrc {
     }
 };
 
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS)
     trace_batch_kernel(SceneDev S, const float4 *__restrict__ org, const float4 *__restrict__ dir, uint32_t n, int any_hit,
                        akb_hit *__restrict__ hits, int32_t *__restrict__ occ, uint32_t *cursor) {
     BatchSrc src{org, dir, S.shading, hits, occ, any_hit != 0};
@@ -396,7 +399,7 @@ template <int SAMP> struct WfSrc {
 };
 
 template <int SAMP>
-__global__ void __launch_bounds__(kBlock) wf_trace_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
+__global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_trace_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
     Counters *ctr = ws.ctr;
     const uint32_t n_ext = ctr->n_ext[b], n_sh = ctr->n_sh[b];
     WfSrc<SAMP> src{S, rc, ws, b, n_ext};
