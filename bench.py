@@ -312,6 +312,14 @@ def main():
                     "note": "BVH traversal is latency/issue/L2-bound, not HBM-streaming-bound; the HBM fraction is low by "
                             "construction (SURVEY.md §8d): ncu_counters carries the issue-slot / pipe / lane figures of the "
                             "same kernel"}
+            # second kernel of the step: wf_shade gathers/scatters path state, 216 algorithmic bytes per shaded vertex
+            # (ray 32 + hit 20 + state 40 read, state 40 + extension ray 32 written, + 52 of the trace)
+            if stp.ms_shade > 0:
+                sb = 164.0 * stp.n_closest_rays + 48.0 * stp.n_shadow_rays  # 216 - the 52 B already counted for the trace kernel
+                roof["shade"] = {"bound": "hbm", "kernel": "wf_shade_kernel (path_vertex per hit, regeneration, film accumulate)",
+                                 "achieved": sb / (stp.ms_shade * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                                 "frac": sb / (stp.ms_shade * 1e-3) / 1e9 / peak,
+                                 "ncu_counters": {k[len("wf_shade_"):]: v for k, v in tj.items() if k.startswith("wf_shade_")}}
         extras = {}
         if not a.no_extras and world == 1:
             extras = ray_microbench(pkg, be, torch)
