@@ -184,6 +184,39 @@ def test_device_bvh_build_same_results(G, S):
         a.close(), b.close()
 
 
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_both_builders_on_triangle_soups_vs_brute_force(seed):
+    """Clustered soups with triangle sizes over four decades, slivers, duplicates and a few scene-sized triangles: the
+    host-built and the device-built tree must both return what a brute-force loop over all triangles returns."""
+    rng = np.random.default_rng(seed)
+    nt = 6000
+    centres = rng.normal(0, 10, (12, 3))
+    c = centres[rng.integers(0, 12, nt)] + rng.normal(0, 1.5, (nt, 3))
+    size = 10 ** rng.uniform(-3, 1, (nt, 1, 1))
+    v = c[:, None, :] + rng.normal(0, 1, (nt, 3, 3)) * size
+    v[:50, 2] = v[:50, 1] + 1e-4 * rng.normal(0, 1, (50, 3))   # slivers
+    v[50:80] = v[100:130]                                      # exact duplicates
+    v[80:84] = rng.uniform(-60, 60, (4, 3, 3))                 # triangles as large as the scene
+    v = v.astype(np.float32)
+    mesh = scenes.AkariMesh(materials=[scenes.DiffuseMaterial(0.5)], vertices=v.reshape(-1, 3),
+                            indices=np.arange(3 * nt, dtype=np.int32), material_indices=np.zeros(nt, np.int32))
+    sc = scenes.Scene(scenes.PerspectiveCamera(fov=60, resolution=(16, 16)), scenes.Path(spp=1, ray_clamp=0.0), [mesh])
+    org, dr = random_rays(rng, 30000, (-25, -25, -25), (25, 25, 25))
+    want = Oracle(sc, brute_force=True).trace(org, dr)
+    dra = dr.copy()
+    dra[:, 3] = 12.0
+    want_occ = Oracle(sc, brute_force=True).trace(org, dra, any_hit=True)
+    assert (want["prim_id"] >= 0).mean() > 0.3
+    for kind in (abi.BVH_HOST_SAH, abi.BVH_DEVICE_LBVH):
+        be = pkg.Backend(sc, 0, bvh_build=kind)
+        assert be.info()["bvh_build"] == kind
+        got = be.trace(org, dr)
+        bad, ties, tb = hit_mismatch(want, got)
+        assert bad == 0 and tb == 0, (kind, bad, ties, tb)
+        assert np.array_equal(be.trace(org, dra, any_hit=True), want_occ), kind
+        be.close()
+
+
 def test_wavefront_equals_megakernel_and_sorting_is_neutral():
     sc = scenes.mixed_box((80, 56), 6, 5)
     be = backend(sc)
