@@ -124,8 +124,8 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
     hs->shading.resize(6 * nt);
     const bool textured = d->n_textures > 0;
     if (textured) hs->tri_tc.resize(2 * nt);
-    std::vector<float> blo(3 * nt), bhi(3 * nt);
-    std::vector<f4> leaf_rec(3 * nt); // flat order first; permuted after the build
+    FloatVec blo(3 * nt), bhi(3 * nt);
+    F4Vec leaf_rec(3 * nt); // flat order first; permuted after the build
     float max_abs = 0;
     struct LightSrc {
         uint64_t tri;

@@ -4,7 +4,9 @@
 // PerspectiveCamera::preprocess (kernel/camera.h:45-59) and `scene.accel = BVHAccelerator; scene.commit()`
 // (core/nodes/scene.cpp:127-135, kernel/scene.cpp:64-81). Pure C++ (no CUDA): api.cu uploads the result to HBM.
 #pragma once
+#include <memory>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/akari_b200.h"
@@ -17,19 +19,35 @@ struct f4 {
     float x, y, z, w;
 };
 
+// std::allocator whose construct() default-initialises, so resize() of a vector that is about to be overwritten
+// (hundreds of MB of per-triangle records) does not first write zeros through one thread.
+template <class T> struct NoInitAlloc : std::allocator<T> {
+    template <class U> struct rebind {
+        using other = NoInitAlloc<U>;
+    };
+    template <class U, class... A> void construct(U *p, A &&...a) {
+        if constexpr (sizeof...(A) == 0)
+            ::new ((void *)p) U;
+        else
+            ::new ((void *)p) U(std::forward<A>(a)...);
+    }
+};
+using F4Vec = std::vector<f4, NoInitAlloc<f4>>;
+using FloatVec = std::vector<float, NoInitAlloc<float>>;
+
 struct HostScene {
     uint64_t n_tris = 0;
     std::vector<uint64_t> geom_offset; // n_meshes + 1
     Bvh8 bvh;
-    std::vector<f4> tris;    // 3 per triangle, leaf order
-    std::vector<f4> shading; // 6 per triangle, flat order
+    F4Vec tris;    // 3 per triangle, leaf order
+    F4Vec shading; // 6 per triangle, flat order
     std::vector<akb_material> mats;
     std::vector<f4> lights; // 4 per light
     // image textures (only filled when the description has any): texels of all textures back to back, per texture
     // (first texel, width, height, 0), per triangle (flat order) and per light the three corner texcoords
     std::vector<f4> texels;
     std::vector<int32_t> tex_info; // 4 per texture
-    std::vector<f4> tri_tc;        // 2 per triangle: (u0,v0,u1,v1) (u2,v2,-,-)
+    F4Vec tri_tc;        // 2 per triangle: (u0,v0,u1,v1) (u2,v2,-,-)
     std::vector<f4> light_tc;      // 2 per light:    (u0,v0,u1,v1) (u2,v2,texture id bits,-)
     std::vector<float> light_func, light_cdf;
     float light_func_int = 0;
