@@ -50,7 +50,7 @@ class Backend:
     `gpu::Integrator::render` (core/nodes/scene.cpp:119-162)."""
 
     def __init__(self, scene, device_index=0, bvh_build=0):
-        """bvh_build: abi.BVH_DEFAULT / BVH_HOST_SAH / BVH_DEVICE_LBVH (include/akari_b200.h akb_bvh_build)."""
+        """bvh_build: abi.BVH_DEFAULT / BVH_HOST_SAH / BVH_DEVICE (include/akari_b200.h akb_bvh_build)."""
         self.lib = init(device_index)
         self.scene = scene
         self.width, self.height = scene.camera.resolution

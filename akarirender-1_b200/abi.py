@@ -14,7 +14,7 @@ INTEGRATOR_PATH, INTEGRATOR_AO = 0, 1
 SAMPLER_LCG, SAMPLER_PCG = 0, 1
 MODE_WAVEFRONT, MODE_MEGAKERNEL = 0, 1
 SPLIT_TILE, SPLIT_SAMPLE = 0, 1
-BVH_DEFAULT, BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1, 2
+BVH_DEFAULT, BVH_HOST_SAH, BVH_DEVICE = 0, 1, 2
 
 
 class Material(C.Structure):

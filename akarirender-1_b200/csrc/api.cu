@@ -253,7 +253,7 @@ akb_status akb_shutdown(void) {
 }
 
 namespace {
-// AKB_BVH_DEVICE_LBVH: csrc/bvh_build.cu, with the host builder as the fallback for trees deeper than the stack
+// AKB_BVH_DEVICE: csrc/bvh_build.cu, with the host builder as the fallback for trees deeper than the stack
 bool device_bvh_builder(const float *lo, const float *hi, size_t n, float pad, int n_threads, Bvh8 *out, std::string *err) {
     const auto t0 = std::chrono::steady_clock::now();
     float node_cost, prim_cost;
@@ -271,11 +271,11 @@ bool device_bvh_builder(const float *lo, const float *hi, size_t n, float pad, i
         build_bvh8(lo, hi, n, pad, n_threads, out);
         return true;
     }
-    out->built_by = AKB_BVH_DEVICE_LBVH;
+    out->built_by = AKB_BVH_DEVICE;
     out->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (getenv("AKB_BVH_VERBOSE"))
-        fprintf(stderr, "[akb] device BVH build: %zu triangles -> %zu nodes, depth %d; upload %.2f sort %.2f tree %.2f fit %.2f emit %.2f download %.2f ms\n",
-                n, out->nodes.size(), out->depth, times.ms_upload, times.ms_sort, times.ms_tree, times.ms_fit, times.ms_emit, times.ms_download);
+        fprintf(stderr, "[akb] device BVH build: %zu triangles -> %zu nodes, depth %d (%s, %d rounds); upload %.2f sort %.2f tree %.2f fit %.2f emit %.2f download %.2f ms\n",
+                n, out->nodes.size(), out->depth, times.ploc_rounds ? "PLOC" : "radix tree", times.ploc_rounds, times.ms_upload, times.ms_sort, times.ms_tree, times.ms_fit, times.ms_emit, times.ms_download);
     return true;
 }
 } // namespace
@@ -296,15 +296,15 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
             for (uint32_t g = 0; g < desc->n_meshes; g++) nt += desc->meshes[g].n_triangles;
         const char *e = getenv("AKB_BVH_BUILD");
         if (e && !strcmp(e, "device"))
-            build = AKB_BVH_DEVICE_LBVH;
+            build = AKB_BVH_DEVICE;
         else if (e && !strcmp(e, "host"))
             build = AKB_BVH_HOST_SAH;
         else
-            build = nt >= (4u << 20) ? AKB_BVH_DEVICE_LBVH : AKB_BVH_HOST_SAH;
+            build = nt >= (4u << 20) ? AKB_BVH_DEVICE : AKB_BVH_HOST_SAH;
     }
-    if (build != AKB_BVH_HOST_SAH && build != AKB_BVH_DEVICE_LBVH) return set_err(AKB_INVALID_ARG, "akb_scene_create: bad bvh_build %d", build);
+    if (build != AKB_BVH_HOST_SAH && build != AKB_BVH_DEVICE) return set_err(AKB_INVALID_ARG, "akb_scene_create: bad bvh_build %d", build);
     const auto t_create = std::chrono::steady_clock::now();
-    st = flatten_scene(desc, 0, &hs, &err, build == AKB_BVH_DEVICE_LBVH ? device_bvh_builder : nullptr);
+    st = flatten_scene(desc, 0, &hs, &err, build == AKB_BVH_DEVICE ? device_bvh_builder : nullptr);
     if (st != AKB_OK) return set_err(st, "%s", err.c_str());
     const auto t_flat = std::chrono::steady_clock::now();
     akb_scene *sc = new akb_scene();

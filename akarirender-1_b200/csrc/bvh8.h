@@ -32,7 +32,7 @@ struct Bvh8 {
     float pad = 0;                   // conservative padding added to every triangle box
     double sah_cost = 0;
     double build_seconds = 0;
-    int built_by = 1; // akb_bvh_build that produced the tree (1 host SAH, 2 device LBVH)
+    int built_by = 1; // akb_bvh_build that produced the tree (1 host SAH, 2 device PLOC)
 };
 
 constexpr int kMaxBvh8Depth = 30; // traverse.cuh keeps a 32-entry stack

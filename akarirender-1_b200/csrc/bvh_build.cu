@@ -1,8 +1,8 @@
 // bvh_build.cu — see bvh_build.cuh. sm_100a only. None of this is on the per-frame path; it is HBM-bound setup
 // work: one radix sort of 12 B per triangle, three passes over ~50 B per binary node, one pass per wide-tree level.
 //
-// Node numbering of the binary radix tree: internal nodes 0 .. n-2 (0 = root), leaf k (k-th triangle in Morton
-// order) = node n-1+k. Binary nodes are never stored as such after the build: only their boxes, ranges and the
+// Node numbering of the binary tree: internal nodes 0 .. n-2 (radix tree: 0 = root; PLOC: in merge order, the last one
+// is the root), leaf k (k-th triangle in Morton order) = node n-1+k. Binary nodes are never stored as such after the build: only their boxes, ranges and the
 // collapse DP tables live in HBM until the wide nodes are emitted.
 #include "bvh_build.cuh"
 
@@ -118,6 +118,103 @@ __global__ void hierarchy_kernel(const uint64_t *__restrict__ keys, int n, int32
     if (i == 0) parent[0] = -1;
 }
 
+struct TreeArrays {
+    int n;
+    int root; // binary node the wide root is rooted at: 0 (radix tree), the last merge (PLOC), n-1 when n == 1
+    int32_t *left, *right, *parent, *first, *count; // internal nodes (parent: all 2n-1 nodes)
+    float4 *nlo, *nhi;                              // all 2n-1 nodes
+    float *cost;                                    // 7 per internal node
+    uint32_t *dp;                                   // per internal node
+    uint32_t *visit;                                // per internal node, zeroed
+    const uint32_t *vals;                           // Morton position -> flat triangle id
+};
+
+// ---- 2b. PLOC (Meister & Bittner 2018, "Parallel Locally-Ordered Clustering for BVH Construction") -------------------
+// Alternative to the radix tree with near-SAH quality: the clusters (initially the triangles in Morton order) each look
+// `radius` positions left and right for the neighbour whose union box has the smallest area; mutual nearest neighbours
+// merge into a new binary node; the array is compacted and the search repeats until one cluster is left. Ties are
+// broken by position, so the globally best pair is always mutual and every round makes progress.
+__global__ void leaf_box_kernel(TreeArrays T, const float *__restrict__ lo, const float *__restrict__ hi, float pad, uint32_t *__restrict__ cluster) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= T.n) return;
+    const size_t t = T.vals[k];
+    float4 blo = make_float4(lo[3 * t] - pad, lo[3 * t + 1] - pad, lo[3 * t + 2] - pad, 0.f);
+    float4 bhi = make_float4(hi[3 * t] + pad, hi[3 * t + 1] + pad, hi[3 * t + 2] + pad, 0.f);
+    if (!(isfinite(blo.x) && isfinite(blo.y) && isfinite(blo.z) && isfinite(bhi.x) && isfinite(bhi.y) && isfinite(bhi.z))) {
+        blo = make_float4(INFINITY, INFINITY, INFINITY, 0.f);
+        bhi = make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f);
+    }
+    T.nlo[T.n - 1 + k] = blo, T.nhi[T.n - 1 + k] = bhi;
+    cluster[k] = (uint32_t)(T.n - 1 + k);
+}
+
+constexpr int kPlocMaxRadius = 32;
+
+__global__ void __launch_bounds__(kThreads) ploc_nearest_kernel(TreeArrays T, const uint32_t *__restrict__ cluster, int c, int radius, int32_t *__restrict__ nn) {
+    __shared__ float4 slo[kThreads + 2 * kPlocMaxRadius], shi[kThreads + 2 * kPlocMaxRadius];
+    const int b0 = blockIdx.x * kThreads;
+    for (int k = threadIdx.x; k < kThreads + 2 * radius; k += kThreads) {
+        const int g = b0 - radius + k;
+        if (g >= 0 && g < c) {
+            const uint32_t id = cluster[g];
+            slo[k] = T.nlo[id], shi[k] = T.nhi[id];
+        }
+    }
+    __syncthreads();
+    const int i = b0 + threadIdx.x;
+    if (i >= c) return;
+    const float4 alo = slo[threadIdx.x + radius], ahi = shi[threadIdx.x + radius];
+    float best = INFINITY;
+    int best_j = -1;
+    unsigned best_key = 0;
+    for (int dj = -radius; dj <= radius; dj++) {
+        const int j = i + dj;
+        if (dj == 0 || j < 0 || j >= c) continue;
+        const float4 blo = slo[threadIdx.x + radius + dj], bhi = shi[threadIdx.x + radius + dj];
+        const float dx = fmaxf(ahi.x, bhi.x) - fminf(alo.x, blo.x), dy = fmaxf(ahi.y, bhi.y) - fminf(alo.y, blo.y),
+                    dz = fmaxf(ahi.z, bhi.z) - fminf(alo.z, blo.z);
+        float a = dx * dy + dy * dz + dz * dx;
+        if (!(a == a)) a = INFINITY; // two empty boxes
+        // ties: a total order on pairs that both ends evaluate alike - nearer positions first, then pairs starting at
+        // an even position (so that runs of identical boxes pair up (0,1)(2,3).. and halve every round)
+        const unsigned key = ((unsigned)abs(dj) << 26) | ((unsigned)(min(i, j) & 1) << 25);
+        if (best_j < 0 || a < best || (a == best && key < best_key)) best = a, best_j = j, best_key = key;
+    }
+    nn[i] = best_j;
+}
+
+// packs (keeps its slot, creates a node) per cluster for one scan: low 32 bits count kept slots, high 32 bits new nodes
+__global__ void ploc_flag_kernel(const int32_t *__restrict__ nn, int c, unsigned long long *__restrict__ flags) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= c) return;
+    const int j = nn[i];
+    const bool mutual = j >= 0 && nn[j] == i;
+    const unsigned long long keep = (!mutual || i < j) ? 1ull : 0ull, make = (mutual && i < j) ? 1ull : 0ull;
+    flags[i] = keep | (make << 32);
+}
+
+__global__ void ploc_merge_kernel(TreeArrays T, const uint32_t *__restrict__ cluster, const int32_t *__restrict__ nn, int c,
+                                  const unsigned long long *__restrict__ flags, const unsigned long long *__restrict__ offs, int next_node,
+                                  uint32_t *__restrict__ cluster_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= c) return;
+    const unsigned long long f = flags[i], o = offs[i];
+    if (!(f & 1ull)) return; // merged into its partner's slot
+    const uint32_t a = cluster[i];
+    uint32_t id = a;
+    if (f >> 32) {
+        const uint32_t b = cluster[nn[i]];
+        const int p = next_node + (int)(o >> 32);
+        const float4 alo = T.nlo[a], ahi = T.nhi[a], blo = T.nlo[b], bhi = T.nhi[b];
+        T.nlo[p] = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.f);
+        T.nhi[p] = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+        T.left[p] = (int32_t)a, T.right[p] = (int32_t)b;
+        T.parent[a] = p, T.parent[b] = p;
+        id = (uint32_t)p;
+    }
+    cluster_out[(uint32_t)o] = id;
+}
+
 // ---- 3. bottom-up: boxes + the optimal 8-wide collapse tables (bvh8.cpp Collapser::solve, same recurrences) ----------
 // dp word per internal node: bits 0-2 split8 (k of C_distribute(n,8)), bit 3 kind (1 = wide node, 0 = leaf slot),
 // bits 4i..4i+2 for i = 1..6: k of the best distribution for i+1 roots (0 = use one root fewer).
@@ -126,15 +223,6 @@ __device__ __forceinline__ float half_area4(float4 lo, float4 hi) {
     return dx * dy + dy * dz + dz * dx;
 }
 
-struct TreeArrays {
-    int n;
-    int32_t *left, *right, *parent, *first, *count; // internal nodes (parent: all 2n-1 nodes)
-    float4 *nlo, *nhi;                              // all 2n-1 nodes
-    float *cost;                                    // 7 per internal node
-    uint32_t *dp;                                   // per internal node
-    uint32_t *visit;                                // per internal node, zeroed
-    const uint32_t *vals;                           // Morton position -> flat triangle id
-};
 
 __global__ void fit_kernel(TreeArrays T, const float *__restrict__ lo, const float *__restrict__ hi, float pad, float node_cost,
                            float prim_cost, int max_leaf) {
@@ -174,7 +262,8 @@ __global__ void fit_kernel(TreeArrays T, const float *__restrict__ lo, const flo
             for (int i = 0; i < 7; i++) cr[i] = __ldcg(&T.cost[7 * (size_t)R + i]);
         }
         const float area = half_area4(nlo, nhi);
-        const int np = T.count[cur];
+        const int np = (L >= n - 1 ? 1 : __ldcg(&T.count[L])) + (R >= n - 1 ? 1 : __ldcg(&T.count[R]));
+        T.count[cur] = np;
         const float c_leaf = np <= max_leaf ? area * (float)np * prim_cost : INFINITY;
         float c[7];
         uint32_t word = 0;
@@ -214,7 +303,22 @@ __global__ void fit_kernel(TreeArrays T, const float *__restrict__ lo, const flo
 __device__ __forceinline__ bool is_tri_node(const TreeArrays &T, int32_t b) { return b >= T.n - 1; }
 __device__ __forceinline__ bool is_leaf_child(const TreeArrays &T, int32_t b) { return is_tri_node(T, b) || !(T.dp[b] & 8u); }
 __device__ __forceinline__ int prims_of(const TreeArrays &T, int32_t b) { return is_tri_node(T, b) ? 1 : T.count[b]; }
-__device__ __forceinline__ int first_of(const TreeArrays &T, int32_t b) { return is_tri_node(T, b) ? b - (T.n - 1) : T.first[b]; }
+// flat ids of the (at most 3) triangles below binary node b, left to right
+__device__ int collect_tris(const TreeArrays &T, int32_t b, uint32_t *out) {
+    int k = 0, sp = 0;
+    int32_t st[4];
+    st[sp++] = b;
+    while (sp > 0 && k < 3) {
+        const int32_t x = st[--sp];
+        if (is_tri_node(T, x)) {
+            out[k++] = T.vals[x - (T.n - 1)];
+        } else {
+            st[sp++] = T.right[x];
+            st[sp++] = T.left[x];
+        }
+    }
+    return k;
+}
 
 // the up-to-8 binary nodes that become the children of the wide node rooted at binary node b (Collapser::gather)
 __device__ int gather_children(const TreeArrays &T, int32_t b, bool root, int32_t *child) {
@@ -353,9 +457,10 @@ __global__ void level_emit_kernel(TreeArrays T, int32_t *__restrict__ item_bnode
         if (i < 0) continue;
         const int32_t c = child[i];
         if (k == 1 || is_leaf_child(T, c)) {
-            const int np = prims_of(T, c), f = first_of(T, c);
+            uint32_t ids[3];
+            const int np = collect_tris(T, c, ids);
             nd.meta[s] = (uint8_t)((((1u << np) - 1u) << 5) | tri_off);
-            for (int j = 0; j < np; j++) tri_order[nd.tri_base + tri_off + j] = T.vals[f + j];
+            for (int j = 0; j < np; j++) tri_order[nd.tri_base + tri_off + j] = ids[j];
             tri_off += (uint32_t)np;
         } else {
             nd.imask |= (uint8_t)(1u << s);
@@ -438,10 +543,25 @@ cudaError_t build_bvh8_device(const float *lo, const float *hi, size_t n_tris, f
     CB(bufs.get(&nodes, n_tris + 1));
     CB(bufs.get(&tri_order, n_tris));
     T.n = n, T.dp = dp, T.visit = visit, T.vals = vals;
-    size_t tmp_sort = 0, tmp_scan = 0;
+    // binary topology: PLOC by default (near-SAH quality), AKB_BVH_DEVICE_ALGO=lbvh for the plain radix tree
+    const char *algo = getenv("AKB_BVH_DEVICE_ALGO");
+    const bool use_ploc = !(algo && !strcmp(algo, "lbvh"));
+    int ploc_radius = 3, ploc_rounds = 0; // measured 1..32 on C3 and a clustered soup: 3-4 is best (profiles/r01c_notes.md)
+    if (const char *e = getenv("AKB_PLOC_RADIUS")) ploc_radius = std::min(kPlocMaxRadius, std::max(1, atoi(e)));
+    uint32_t *cluster_a = nullptr, *cluster_b = nullptr;
+    int32_t *nn = nullptr;
+    unsigned long long *ploc_offs = nullptr;
+    if (use_ploc) {
+        CB(bufs.get(&cluster_a, n_tris));
+        CB(bufs.get(&cluster_b, n_tris));
+        CB(bufs.get(&nn, n_tris));
+        CB(bufs.get(&ploc_offs, n_tris));
+    }
+    size_t tmp_sort = 0, tmp_scan = 0, tmp_scan64 = 0;
     CB(cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort, keys_in, keys, vals_in, vals, n, 0, 63));
     CB(cub::DeviceScan::ExclusiveSum(nullptr, tmp_scan, n_int, off_int, n));
-    const size_t tmp_bytes = std::max(tmp_sort, tmp_scan);
+    CB(cub::DeviceScan::ExclusiveSum(nullptr, tmp_scan64, (unsigned long long *)nullptr, (unsigned long long *)nullptr, n));
+    const size_t tmp_bytes = std::max(std::max(tmp_sort, tmp_scan), tmp_scan64);
     uint8_t *tmp;
     CB(bufs.get(&tmp, tmp_bytes));
 
@@ -458,14 +578,42 @@ cudaError_t build_bvh8_device(const float *lo, const float *hi, size_t n_tris, f
     CB(cudaEventRecord(ev[2]));
     CB(cudaMemsetAsync(T.parent, 0xFF, 2 * n_tris * sizeof(int32_t)));
     CB(cudaMemsetAsync(visit, 0, n_tris * sizeof(uint32_t)));
-    if (n > 1) hierarchy_kernel<<<blocks_for(n_tris - 1), kThreads>>>(keys, n, T.left, T.right, T.parent, T.first, T.count);
+    T.root = 0; // also right for n == 1, where node 0 is the only triangle
+    if (n > 1 && !use_ploc) hierarchy_kernel<<<blocks_for(n_tris - 1), kThreads>>>(keys, n, T.left, T.right, T.parent, T.first, T.count);
+    if (n > 1 && use_ploc) {
+        uint32_t *ca = cluster_a, *cb2 = cluster_b;
+        leaf_box_kernel<<<blocks_for(n_tris), kThreads>>>(T, d_lo, d_hi, pad, ca);
+        unsigned long long *flags = (unsigned long long *)keys_in; // the unsorted keys are dead by now
+        int c = n, next_node = 0;
+        while (c > 1) {
+            ploc_nearest_kernel<<<blocks_for((size_t)c), kThreads>>>(T, ca, c, ploc_radius, nn);
+            ploc_flag_kernel<<<blocks_for((size_t)c), kThreads>>>(nn, c, flags);
+            tb = tmp_bytes;
+            CB(cub::DeviceScan::ExclusiveSum(tmp, tb, flags, ploc_offs, c));
+            unsigned long long last[2];
+            CB(cudaMemcpyAsync(&last[0], flags + (c - 1), 8, cudaMemcpyDeviceToHost));
+            CB(cudaMemcpyAsync(&last[1], ploc_offs + (c - 1), 8, cudaMemcpyDeviceToHost));
+            CB(cudaStreamSynchronize(0));
+            const unsigned long long tot = last[0] + last[1];
+            const int kept = (int)(tot & 0xFFFFFFFFull), made = (int)(tot >> 32);
+            if (made <= 0 || kept != c - made || next_node + made > n - 1) { // cannot happen: the best pair is always mutual
+                done();
+                return cudaErrorUnknown;
+            }
+            ploc_merge_kernel<<<blocks_for((size_t)c), kThreads>>>(T, ca, nn, c, flags, ploc_offs, next_node, cb2);
+            next_node += made, c = kept;
+            std::swap(ca, cb2);
+            ploc_rounds++;
+        }
+        T.root = next_node - 1;
+    }
     CB(cudaEventRecord(ev[3]));
     fit_kernel<<<blocks_for(n_tris), kThreads>>>(T, d_lo, d_hi, pad, node_cost, prim_cost, max_leaf);
     CB(cudaEventRecord(ev[4]));
     CB(cudaGetLastError());
     float4 root_box[2];
-    CB(cudaMemcpy(&root_box[0], T.nlo, sizeof(float4), cudaMemcpyDeviceToHost));
-    CB(cudaMemcpy(&root_box[1], T.nhi, sizeof(float4), cudaMemcpyDeviceToHost));
+    CB(cudaMemcpy(&root_box[0], T.nlo + T.root, sizeof(float4), cudaMemcpyDeviceToHost));
+    CB(cudaMemcpy(&root_box[1], T.nhi + T.root, sizeof(float4), cudaMemcpyDeviceToHost));
     if (!(isfinite(root_box[0].x) && isfinite(root_box[0].y) && isfinite(root_box[0].z) && isfinite(root_box[1].x) &&
           isfinite(root_box[1].y) && isfinite(root_box[1].z))) {
         *fallback = true;
@@ -473,7 +621,8 @@ cudaError_t build_bvh8_device(const float *lo, const float *hi, size_t n_tris, f
         return cudaSuccess;
     }
     // wide nodes, level by level; item w = wide node w, item_bnode[w] = the binary node it is rooted at
-    CB(cudaMemsetAsync(item_bnode, 0, sizeof(int32_t)));
+    const int32_t root_item = T.root;
+    CB(cudaMemcpyAsync(item_bnode, &root_item, sizeof(int32_t), cudaMemcpyHostToDevice));
     uint32_t begin = 0, end = 1, tri_total = 0;
     int depth = 0;
     while (begin < end) {
@@ -518,6 +667,7 @@ cudaError_t build_bvh8_device(const float *lo, const float *hi, size_t n_tris, f
     out->pad = pad;
     out->sah_cost = 0;
     if (times) {
+        times->ploc_rounds = ploc_rounds;
         cudaEventElapsedTime(&times->ms_upload, ev[0], ev[1]);
         cudaEventElapsedTime(&times->ms_sort, ev[1], ev[2]);
         cudaEventElapsedTime(&times->ms_tree, ev[2], ev[3]);

@@ -2,7 +2,8 @@
 //
 // Replaces, for large scenes, the host build of bvh8.cpp (itself the replacement of the reference's
 // TBVHAccelerator constructor, kernel/bvh-accelerator.h:72-87,125-475: 3.4 s per 1 M triangles on 8 cores): Morton
-// order + Karras' binary radix tree + bottom-up box fit fused with the optimal 8-wide collapse DP + level-by-level
+// order + binary topology by locally-ordered clustering (PLOC, Meister & Bittner 2018; or Karras' binary radix tree
+// with AKB_BVH_DEVICE_ALGO=lbvh) + bottom-up box fit fused with the optimal 8-wide collapse DP + level-by-level
 // emission of the same 80-byte nodes (bvh8.h). The result is a different tree from the host build's, which is
 // allowed by the traversal's result contract (traverse.h: nearest t over all triangles, lowest flat id among equal t
 // - independent of the tree), so films and hits stay bit-identical up to the ill-conditioned grazing tests described
@@ -16,6 +17,7 @@ namespace akb {
 
 struct DeviceBuildTimes {
     float ms_upload = 0, ms_sort = 0, ms_tree = 0, ms_fit = 0, ms_emit = 0, ms_download = 0;
+    int ploc_rounds = 0; // 0: radix tree
 };
 
 // lo/hi: n x 3 host triangle boxes (unpadded; `pad` is added on the device as build_bvh8 does). Fills out->nodes,

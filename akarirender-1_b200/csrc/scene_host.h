@@ -56,7 +56,7 @@ struct HostScene {
 
 // Returns AKB_OK or AKB_INVALID_ARG (+ message).
 // `builder` (optional): builds the BVH from the unpadded triangle boxes instead of build_bvh8 (api.cu passes the
-// device builder for AKB_BVH_DEVICE_LBVH); it returns false (+ message) on failure.
+// device builder for AKB_BVH_DEVICE); it returns false (+ message) on failure.
 typedef bool (*BvhBuilder)(const float *lo, const float *hi, size_t n, float pad, int n_threads, Bvh8 *out, std::string *err);
 akb_status flatten_scene(const akb_scene_desc *desc, int n_threads, HostScene *out, std::string *err, BvhBuilder builder = nullptr);
 

@@ -45,7 +45,7 @@ int main(int argc, char **argv) {
         else if (a == "--pfm") pfm = next();
         else if (a == "--bvh") {
             const std::string v = next();
-            bvh = v == "host" ? AKB_BVH_HOST_SAH : (v == "device" ? AKB_BVH_DEVICE_LBVH : AKB_BVH_DEFAULT);
+            bvh = v == "host" ? AKB_BVH_HOST_SAH : (v == "device" ? AKB_BVH_DEVICE : AKB_BVH_DEFAULT);
         }
         else if (a == "-o" || a == "--output") output = next();
         else if (a == "-i" || a == "--input") input = next();
@@ -73,7 +73,7 @@ int main(int argc, char **argv) {
     CHECK(akb_scene_create(desc, &scene));
     printf("building acceleration structure took (%.3fs): %llu triangles, %llu BVH8 nodes (%s build, %.3fs), %llu lights\n", now_s() - t,
            (unsigned long long)akb_scene_info(scene, 0), (unsigned long long)akb_scene_info(scene, 1),
-           akb_scene_info(scene, 7) == AKB_BVH_DEVICE_LBVH ? "device" : "host", akb_scene_info(scene, 6) * 1e-6,
+           akb_scene_info(scene, 7) == AKB_BVH_DEVICE ? "device" : "host", akb_scene_info(scene, 6) * 1e-6,
            (unsigned long long)akb_scene_info(scene, 3));
     std::vector<float> film((size_t)W * H * 4);
     akb_render_stats st;

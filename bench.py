@@ -144,7 +144,7 @@ def main():
                     help="N>1: how ranks share the frame (akb_split). auto = sample split (every GPU keeps a full-size "
                          "wavefront; statistically equivalent film), with the bit-identical tile split timed beside it")
     ap.add_argument("--bvh", default="default", choices=["default", "host", "device"],
-                    help="akb_bvh_build: library default (host SAH below 4 Mi triangles, device LBVH above), or force one")
+                    help="akb_bvh_build: library default (host SAH below 4 Mi triangles, device PLOC above), or force one")
     ap.add_argument("--spp", type=int, default=0)
     ap.add_argument("--mode", default="wavefront", choices=["wavefront", "megakernel"])
     ap.add_argument("--cpu-rows", type=int, default=24)
@@ -338,7 +338,7 @@ def main():
                            if world > 1 else "single", "tile": 32, "l2": "inputs larger than L2: BVH+triangles %.0f MB, shading records %.0f MB, path state %.0f MB"
                            % ((info["bvh_bytes"] + info["triangle_bytes"]) / 1e6, info["n_triangles"] * 96 / 1e6, W * H * 208 / 1e6),
                            "bvh_nodes": info["n_bvh_nodes"], "scene_build_s": round(build_s, 2),
-                           "bvh_build": {1: "host SAH", 2: "device LBVH"}.get(info["bvh_build"]), "bvh_build_s": round(info["build_us"] / 1e6, 3)},
+                           "bvh_build": {1: "host SAH", 2: "device PLOC"}.get(info["bvh_build"]), "bvh_build_s": round(info["build_us"] / 1e6, 3)},
                 "clocks": clk,
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": C.sizeof(pkg.abi.RenderParams),
                         "d2h_bytes_per_step": W * H * 16,
@@ -484,7 +484,7 @@ def bench_c2(pkg, a, emit, local, torch):
             "config": {"workload": "C2: %d coherent + %d incoherent rays vs the 999700-triangle mesh M1 (closest hit; any hit with tmax 50 beside it)" % (n, n),
                        "l2": "inputs larger than L2: %.1f GB of rays + %.1f GB of hits per set" % (n * 32 / 1e9, n * 20 / 1e9),
                        "bvh_nodes": info["n_bvh_nodes"], "scene_build_s": round(build_s, 2),
-                       "bvh_build": {1: "host SAH", 2: "device LBVH"}.get(info["bvh_build"]), "bvh_build_s": round(info["build_us"] / 1e6, 3),
+                       "bvh_build": {1: "host SAH", 2: "device PLOC"}.get(info["bvh_build"]), "bvh_build_s": round(info["build_us"] / 1e6, 3),
                        "primary_hit_fraction": hit_frac},
             "clocks": clk,
             "e2e": {"value": m / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": m * 32, "d2h_bytes_per_step": m * 20,

@@ -101,12 +101,13 @@ typedef struct akb_camera {
  * (a grazing ray with |a| barely above the 1e-6 reject can "hit" a triangle at a computed point outside the
  * triangle's box: whether any tree - the reference's own included - reaches that test depends on its boxes; measured
  * about 2.5e-8 of rays on C3). The choices differ in build time and traversal speed.
- *   DEFAULT: AKB_BVH_BUILD=host|device in the environment, else HOST_SAH below 4 Mi triangles and DEVICE_LBVH from
+ *   DEFAULT: AKB_BVH_BUILD=host|device in the environment, else HOST_SAH below 4 Mi triangles and DEVICE from
  *            there on (where the host build takes seconds).
  *   HOST_SAH: binned-SAH binary build on the host threads + optimal 8-wide collapse (csrc/bvh8.cpp).
- *   DEVICE_LBVH: Morton order + binary radix tree + the same collapse, all on the GPU (csrc/bvh_build.cu);
- *                falls back to HOST_SAH when the tree would be deeper than the traversal stack. */
-typedef enum akb_bvh_build { AKB_BVH_DEFAULT = 0, AKB_BVH_HOST_SAH = 1, AKB_BVH_DEVICE_LBVH = 2 } akb_bvh_build;
+ *   DEVICE: Morton order + locally-ordered clustering (PLOC; AKB_BVH_DEVICE_ALGO=lbvh for the plain binary radix
+ *           tree) + the same collapse, all on the GPU (csrc/bvh_build.cu); falls back to HOST_SAH when the tree
+ *           would be deeper than the traversal stack. */
+typedef enum akb_bvh_build { AKB_BVH_DEFAULT = 0, AKB_BVH_HOST_SAH = 1, AKB_BVH_DEVICE = 2 } akb_bvh_build;
 
 typedef struct akb_scene_desc {
     uint32_t abi_version; /* AKB_ABI_VERSION */

@@ -147,13 +147,13 @@ def test_both_traversal_steps_bit_identical(G, S, name):
 
 
 def test_device_bvh_build_same_results(G, S):
-    """akb_bvh_build DEVICE_LBVH (csrc/bvh_build.cu) builds another tree; the traversal's result contract does not
+    """akb_bvh_build DEVICE (csrc/bvh_build.cu) builds another tree; the traversal's result contract does not
     depend on the tree, so hits, occlusion and films must match the golden vectors / the host-built tree bit for bit."""
     for name in ("cornell", "terrain"):
         sc = S[name]
-        be = pkg.Backend(sc, 0, bvh_build=abi.BVH_DEVICE_LBVH)
+        be = pkg.Backend(sc, 0, bvh_build=abi.BVH_DEVICE)
         info = be.info()
-        assert info["bvh_build"] == abi.BVH_DEVICE_LBVH and 1 <= info["bvh_depth"] <= 30, info
+        assert info["bvh_build"] == abi.BVH_DEVICE and 1 <= info["bvh_depth"] <= 30, info
         for sfx in ("", "2"):
             h = be.trace(G[f"{name}_org{sfx}"], G[f"{name}_dir{sfx}"])
             bad, ties, tb = hit_mismatch(G[f"{name}_hits{sfx}"], h)
@@ -176,8 +176,8 @@ def test_device_bvh_build_same_results(G, S):
                                 indices=np.arange(3 * nt, dtype=np.int32), material_indices=np.zeros(nt, np.int32))
         sc = scenes.Scene(scenes.PerspectiveCamera(fov=60, resolution=(16, 16)), scenes.Path(spp=1, ray_clamp=0.0), [mesh])
         org, dr = random_rays(rng, 20000, (-2, -2, -2), (2, 2, 2))
-        a, b = pkg.Backend(sc, 0, bvh_build=abi.BVH_DEVICE_LBVH), backend(sc)
-        assert a.info()["bvh_build"] == abi.BVH_DEVICE_LBVH
+        a, b = pkg.Backend(sc, 0, bvh_build=abi.BVH_DEVICE), backend(sc)
+        assert a.info()["bvh_build"] == abi.BVH_DEVICE
         ha, hb = a.trace(org, dr), b.trace(org, dr)
         assert ha.tobytes() == hb.tobytes(), nt
         assert (ha["prim_id"] >= 0).sum() > 0
@@ -207,7 +207,7 @@ def test_both_builders_on_triangle_soups_vs_brute_force(seed):
     dra[:, 3] = 12.0
     want_occ = Oracle(sc, brute_force=True).trace(org, dra, any_hit=True)
     assert (want["prim_id"] >= 0).mean() > 0.3
-    for kind in (abi.BVH_HOST_SAH, abi.BVH_DEVICE_LBVH):
+    for kind in (abi.BVH_HOST_SAH, abi.BVH_DEVICE):
         be = pkg.Backend(sc, 0, bvh_build=kind)
         assert be.info()["bvh_build"] == kind
         got = be.trace(org, dr)

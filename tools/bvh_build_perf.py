@@ -1,4 +1,4 @@
-"""Host SAH build vs device LBVH build: build time, tree size and traversal speed on the same scene.
+"""Host SAH build vs device PLOC build: build time, tree size and traversal speed on the same scene.
 Development aid; run on the GPU box: python tools/bvh_build_perf.py [c3|c4]"""
 import importlib
 import os
@@ -24,7 +24,7 @@ def main():
     W, H = sc.camera.resolution
     film = torch.zeros(H * W * 4, dtype=torch.float32, device="cuda")
     films = []
-    for name, kind in (("host SAH", abi.BVH_HOST_SAH), ("device LBVH", abi.BVH_DEVICE_LBVH), ("device LBVH (2nd)", abi.BVH_DEVICE_LBVH)):
+    for name, kind in (("host SAH", abi.BVH_HOST_SAH), ("device PLOC", abi.BVH_DEVICE), ("device PLOC (2nd)", abi.BVH_DEVICE)):
         t = time.time()
         be = pkg.Backend(sc, 0, bvh_build=kind)
         create_s = time.time() - t

@@ -14,7 +14,7 @@ abi, scenes = pkg.abi, pkg.scenes
 def main():
     sc = scenes.terrain_scene(n=708, resolution=(1920, 1080), spp=1, max_depth=8, materials="c3")
     a = pkg.Backend(sc, 0, bvh_build=abi.BVH_HOST_SAH)
-    b = pkg.Backend(sc, 0, bvh_build=abi.BVH_DEVICE_LBVH)
+    b = pkg.Backend(sc, 0, bvh_build=abi.BVH_DEVICE)
     W, H = 1920, 1080
     ys, xs = np.mgrid[0:H, 0:W]
     xy = np.stack([xs.ravel(), ys.ravel()], -1).astype(np.int32)
