@@ -289,8 +289,9 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
     std::string err;
     int build = desc ? (int)desc->bvh_build : 0;
     if (build == AKB_BVH_DEFAULT) {
-        // host SAH for scenes it builds in about a second, the device build above that (measured on B200, C4's 10 M
-        // triangles: 4.4 s vs 0.17 s to build, 5 % slower to traverse; C3's 1 M: 0.43 s vs 0.02 s, same speed)
+        // host SAH for scenes it builds in about a second, the device build above that (measured on B200: C3's 1 M
+        // triangles 0.43 s vs 0.03 s to build but 1 % slower to render (C5: 2 %); C4's 10 M: 4.4 s vs 0.08 s, 2.4 %
+        // slower; a 1 M-triangle clustered soup: 0.9 s vs 0.03 s, 1-8 % FASTER to traverse)
         uint64_t nt = 0;
         if (desc && desc->meshes)
             for (uint32_t g = 0; g < desc->n_meshes; g++) nt += desc->meshes[g].n_triangles;

@@ -160,7 +160,7 @@ def test_device_bvh_build_same_results(G, S):
             assert bad == 0 and tb == 0, (name, sfx, bad, ties, tb)
         occ = be.trace(G[f"{name}_org2"], G[f"{name}_dir2_any"], any_hit=True)
         assert np.array_equal(occ, G[f"{name}_occ2"])
-        ref = backend(sc)
+        ref = pkg.Backend(sc, 0, bvh_build=abi.BVH_HOST_SAH)
         assert ref.info()["bvh_build"] == abi.BVH_HOST_SAH
         assert same_bits(be.render()[0], ref.render()[0])
         be.close(), ref.close()
@@ -176,7 +176,7 @@ def test_device_bvh_build_same_results(G, S):
                                 indices=np.arange(3 * nt, dtype=np.int32), material_indices=np.zeros(nt, np.int32))
         sc = scenes.Scene(scenes.PerspectiveCamera(fov=60, resolution=(16, 16)), scenes.Path(spp=1, ray_clamp=0.0), [mesh])
         org, dr = random_rays(rng, 20000, (-2, -2, -2), (2, 2, 2))
-        a, b = pkg.Backend(sc, 0, bvh_build=abi.BVH_DEVICE), backend(sc)
+        a, b = pkg.Backend(sc, 0, bvh_build=abi.BVH_DEVICE), pkg.Backend(sc, 0, bvh_build=abi.BVH_HOST_SAH)
         assert a.info()["bvh_build"] == abi.BVH_DEVICE
         ha, hb = a.trace(org, dr), b.trace(org, dr)
         assert ha.tobytes() == hb.tobytes(), nt
