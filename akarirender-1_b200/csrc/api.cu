@@ -25,6 +25,7 @@ int g_n_sms = 0;
 constexpr size_t kMaxBatch = (size_t)1 << 30;
 bool g_profile_stages = false;
 size_t g_trace_chunk = (size_t)1 << 21; // AKB_TRACE_CHUNK: rays per staging slot of akb_trace (host batches)
+int g_poll_lag = 1;                    // AKB_POLL_LAG=0: wait for every queue-length poll (tuning aid)
 int g_pipelines = 2;                   // AKB_PIPELINES: half-frame pipelines of the wavefront (1 or 2)
 int g_pipeline_min_slots = 128 * 1024; // AKB_PIPELINE_MIN_SLOTS: below this one pipeline keeps the launches large
 
@@ -66,7 +67,7 @@ struct akb_scene {
     int ws_slots = 0;
     Counters *d_ctr = nullptr, *h_ctr = nullptr; // [2]: one per half-frame pipeline
     cudaStream_t aux_stream = nullptr;           // second pipeline's stream
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_poll[2] = {nullptr, nullptr};
     float4 *d_film = nullptr;
     size_t d_film_px = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -109,6 +110,8 @@ struct akb_scene {
         if (aux_stream) cudaStreamDestroy(aux_stream);
         if (ev_fork) cudaEventDestroy(ev_fork);
         if (ev_join) cudaEventDestroy(ev_join);
+        for (cudaEvent_t e : ev_poll)
+            if (e) cudaEventDestroy(e);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
     }
@@ -232,6 +235,7 @@ akb_status akb_init(int device_index) {
     const char *pf = getenv("AKB_PROFILE_STAGES");
     g_profile_stages = pf && pf[0] == '1';
     if (const char *e = getenv("AKB_PIPELINES")) g_pipelines = atoi(e);
+    if (const char *e = getenv("AKB_POLL_LAG")) g_poll_lag = atoi(e) != 0;
     if (const char *e = getenv("AKB_TRACE_CHUNK")) g_trace_chunk = std::max<size_t>(1024, (size_t)atoll(e));
     if (const char *e = getenv("AKB_PIPELINE_MIN_SLOTS")) g_pipeline_min_slots = atoi(e);
     if (const char *rb = getenv("AKB_REFILL_BELOW")) {
@@ -339,6 +343,8 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&sc->aux_stream, cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_fork, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_join, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_poll[0], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_poll[1], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreate(&sc->ev0);
         if (e == cudaSuccess) e = cudaEventCreate(&sc->ev1);
         if (e != cudaSuccess) st = set_err(AKB_CUDA_ERROR, "akb_scene_create: %s", cudaGetErrorString(e));
@@ -455,7 +461,8 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
             launches++;
         }
         const long max_it = (long)rc.spp * (rc.max_depth + 2) + 2;
-        const int check_every = 4;
+        const int check_every = 4; // even: a snapshot taken after an odd bounce is read after an odd bounce
+        bool poll_pending[2] = {false, false};
         auto mark = [&]() {
             if (!g_profile_stages) return cudaSuccess;
             cudaEvent_t e;
@@ -480,13 +487,27 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
                 }
             CU(mark());
             if ((it % check_every) == check_every - 1) {
-                for (int q = 0; q < n_pipes; q++)
-                    if (pipe[q].live) CU(cudaMemcpyAsync(sc->h_ctr + q, sc->d_ctr + q, sizeof(Counters), cudaMemcpyDeviceToHost, pipe[q].st));
-                for (int q = 0; q < n_pipes; q++)
-                    if (pipe[q].live) {
-                        CU(cudaStreamSynchronize(pipe[q].st));
+                // The queue lengths are read one poll late: the copy issued here is looked at only after the next
+                // check_every bounces have been enqueued, so the GPU never idles while the host waits for it. A
+                // finished pipeline runs at most check_every more bounces on empty queues (microseconds).
+                for (int q = 0; q < n_pipes; q++) {
+                    if (!pipe[q].live) continue;
+                    if (poll_pending[q] || !g_poll_lag) {
+                        if (!g_poll_lag) {
+                            CU(cudaMemcpyAsync(sc->h_ctr + q, sc->d_ctr + q, sizeof(Counters), cudaMemcpyDeviceToHost, pipe[q].st));
+                            CU(cudaStreamSynchronize(pipe[q].st));
+                        } else {
+                            CU(cudaEventSynchronize(sc->ev_poll[q]));
+                        }
+                        poll_pending[q] = false;
                         if (sc->h_ctr[q].n_ext[b ^ 1] == 0 && sc->h_ctr[q].n_sh[b ^ 1] == 0) pipe[q].live = false;
                     }
+                    if (pipe[q].live && g_poll_lag) {
+                        CU(cudaMemcpyAsync(sc->h_ctr + q, sc->d_ctr + q, sizeof(Counters), cudaMemcpyDeviceToHost, pipe[q].st));
+                        CU(cudaEventRecord(sc->ev_poll[q], pipe[q].st));
+                        poll_pending[q] = true;
+                    }
+                }
             }
         }
         if (n_pipes == 2) {
