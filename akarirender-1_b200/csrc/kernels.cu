@@ -50,6 +50,22 @@ __device__ __forceinline__ void queue_push(bool pred, uint32_t value, uint32_t *
     if (pred) queue[base + __popc(m & lanemask_lt())] = value;
 }
 
+// Two appends at once (the shade step's extension and shadow queues): lanes 0 and 1 issue the two atomics in ONE
+// instruction, so the warp waits for one round trip to L2 instead of two.
+__device__ __forceinline__ void queue_push2(bool p0, uint32_t v0, uint32_t *q0, uint32_t *c0, bool p1, uint32_t v1, uint32_t *q1,
+                                            uint32_t *c1) {
+    const unsigned m0 = __ballot_sync(0xffffffffu, p0), m1 = __ballot_sync(0xffffffffu, p1);
+    if ((m0 | m1) == 0) return;
+    const unsigned lane = threadIdx.x & 31;
+    uint32_t *ctr = lane == 0 ? c0 : c1;
+    const uint32_t cnt = (uint32_t)__popc(lane == 0 ? m0 : m1);
+    uint32_t base = 0;
+    if (lane < 2 && cnt) base = atomicAdd(ctr, cnt);
+    const uint32_t b0 = __shfl_sync(0xffffffffu, base, 0), b1 = __shfl_sync(0xffffffffu, base, 1);
+    if (p0) q0[b0 + __popc(m0 & lanemask_lt())] = v0;
+    if (p1) q1[b1 + __popc(m1 & lanemask_lt())] = v1;
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void selftest_kernel(int *result, float a, float b, float c) {
     // (1+2^-12)^2 = 1 + 2^-11 + 2^-24 rounds to 1 + 2^-11, so a*b + c == 0 unless the compiler fused it (2^-24).
@@ -511,8 +527,7 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
                 }
             }
         }
-        queue_push(push_ext, ext_entry, ws.q_ext[b ^ 1], &ctr->n_ext[b ^ 1]);
-        queue_push(push_sh, slot, ws.q_sh[b ^ 1], &ctr->n_sh[b ^ 1]);
+        queue_push2(push_ext, ext_entry, ws.q_ext[b ^ 1], &ctr->n_ext[b ^ 1], push_sh, slot, ws.q_sh[b ^ 1], &ctr->n_sh[b ^ 1]);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
 #pragma unroll
