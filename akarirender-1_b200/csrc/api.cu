@@ -25,6 +25,8 @@ int g_n_sms = 0;
 constexpr size_t kMaxBatch = (size_t)1 << 30;
 bool g_profile_stages = false;
 size_t g_trace_chunk = (size_t)1 << 21; // AKB_TRACE_CHUNK: rays per staging slot of akb_trace (host batches)
+int g_check_every = 4;                 // AKB_CHECK_EVERY: bounces per graph launch / queue-length poll (even)
+int g_graphs = 1;                      // AKB_GRAPHS=0: launch every bounce's kernels one by one (tuning aid)
 int g_poll_lag = 1;                    // AKB_POLL_LAG=0: wait for every queue-length poll (tuning aid)
 int g_pipelines = 2;                   // AKB_PIPELINES: half-frame pipelines of the wavefront (1 or 2)
 int g_pipeline_min_slots = 128 * 1024; // AKB_PIPELINE_MIN_SLOTS: below this one pipeline keeps the launches large
@@ -81,6 +83,21 @@ struct akb_scene {
         cudaStream_t st = nullptr;
     } trace_slot[2];
     size_t trace_cap = 0; // rays per slot
+    // one CUDA graph per half-frame pipeline: check_every bounces (trace + shade each) of the wavefront loop, captured
+    // once and relaunched for the whole frame (and later frames with the same parameters)
+    struct BounceGraph {
+        cudaGraphExec_t exec = nullptr;
+        RenderConfig rc;
+        Workspace ws;
+        int n_bounces = 0;
+    } bounce_graph[2];
+    cudaStream_t cap_stream = nullptr;
+    void free_graphs() {
+        for (BounceGraph &g : bounce_graph) {
+            if (g.exec) cudaGraphExecDestroy(g.exec);
+            g.exec = nullptr;
+        }
+    }
 
     void free_trace() {
         for (TraceSlot &t : trace_slot) {
@@ -101,6 +118,8 @@ struct akb_scene {
         ws_slots = 0;
     }
     ~akb_scene() {
+        free_graphs();
+        if (cap_stream) cudaStreamDestroy(cap_stream);
         free_ws();
         free_trace();
         for (void *p : allocs) cudaFree(p);
@@ -236,6 +255,8 @@ akb_status akb_init(int device_index) {
     g_profile_stages = pf && pf[0] == '1';
     if (const char *e = getenv("AKB_PIPELINES")) g_pipelines = atoi(e);
     if (const char *e = getenv("AKB_POLL_LAG")) g_poll_lag = atoi(e) != 0;
+    if (const char *e = getenv("AKB_GRAPHS")) g_graphs = atoi(e) != 0;
+    if (const char *e = getenv("AKB_CHECK_EVERY")) g_check_every = std::max(2, atoi(e) & ~1);
     if (const char *e = getenv("AKB_TRACE_CHUNK")) g_trace_chunk = std::max<size_t>(1024, (size_t)atoll(e));
     if (const char *e = getenv("AKB_PIPELINE_MIN_SLOTS")) g_pipeline_min_slots = atoi(e);
     if (const char *rb = getenv("AKB_REFILL_BELOW")) {
@@ -343,6 +364,7 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&sc->aux_stream, cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_fork, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_join, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&sc->cap_stream, cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_poll[0], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_poll[1], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreate(&sc->ev0);
@@ -415,6 +437,7 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
     if ((tile & (tile - 1)) != 0 || tile < 8 || tile > 1024) return set_err(AKB_INVALID_ARG, "akb_render_device: tile_size must be a power of two in [8,1024]");
     cudaStream_t stream = (cudaStream_t)cuda_stream;
     RenderConfig rc;
+    memset(&rc, 0, sizeof rc); // compared bytewise with the cached graphs' copy
     if (p->split != AKB_SPLIT_TILE && p->split != AKB_SPLIT_SAMPLE) return set_err(AKB_INVALID_ARG, "akb_render_device: bad split %d", p->split);
     const Shard shard = make_shard(sc->width, sc->height, p);
     rc.spp = shard.spp, rc.max_depth = p->max_depth, rc.rr_start = p->rr_start_depth, rc.sampler = p->sampler;
@@ -461,7 +484,7 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
             launches++;
         }
         const long max_it = (long)rc.spp * (rc.max_depth + 2) + 2;
-        const int check_every = 4; // even: a snapshot taken after an odd bounce is read after an odd bounce
+        const int check_every = g_check_every; // even: a snapshot taken after an odd bounce is read after an odd bounce
         bool poll_pending[2] = {false, false};
         auto mark = [&]() {
             if (!g_profile_stages) return cudaSuccess;
@@ -472,20 +495,50 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
             return cudaEventRecord(e, stream);
         };
         CU(mark());
+        const bool use_graphs = g_graphs && !g_profile_stages;
+        if (use_graphs)
+            for (int q = 0; q < n_pipes; q++) {
+                akb_scene::BounceGraph &g = sc->bounce_graph[q];
+                if (g.exec && g.n_bounces == check_every && !memcmp(&g.rc, &rc, sizeof rc) && !memcmp(&g.ws, &pipe[q].ws, sizeof(Workspace))) continue;
+                if (g.exec) cudaGraphExecDestroy(g.exec);
+                g.exec = nullptr;
+                CU(cudaStreamBeginCapture(sc->cap_stream, cudaStreamCaptureModeThreadLocal));
+                cudaError_t ce = cudaSuccess;
+                for (int k = 0; k < check_every && ce == cudaSuccess; k++) {
+                    ce = launch_wf_trace(sc->dev, rc, pipe[q].ws, k & 1, g_n_sms, sc->cap_stream);
+                    if (ce == cudaSuccess) ce = launch_wf_shade(sc->dev, rc, pipe[q].ws, k & 1, g_n_sms, sc->cap_stream);
+                }
+                cudaGraph_t graph = nullptr;
+                const cudaError_t ee = cudaStreamEndCapture(sc->cap_stream, &graph);
+                if (ce == cudaSuccess) ce = ee;
+                if (ce == cudaSuccess) ce = cudaGraphInstantiate(&g.exec, graph, 0);
+                if (graph) cudaGraphDestroy(graph);
+                CU(ce);
+                g.rc = rc, g.ws = pipe[q].ws, g.n_bounces = check_every;
+            }
         for (long it = 0; it < max_it && (pipe[0].live || pipe[1].live); it++) {
             const int b = (int)(it & 1);
-            for (int q = 0; q < n_pipes; q++)
-                if (pipe[q].live) {
-                    CU(launch_wf_trace(sc->dev, rc, pipe[q].ws, b, g_n_sms, pipe[q].st));
-                    launches++;
-                }
-            CU(mark());
-            for (int q = 0; q < n_pipes; q++)
-                if (pipe[q].live) {
-                    CU(launch_wf_shade(sc->dev, rc, pipe[q].ws, b, g_n_sms, pipe[q].st));
-                    launches++;
-                }
-            CU(mark());
+            if (use_graphs) {
+                if ((it % check_every) == 0)
+                    for (int q = 0; q < n_pipes; q++)
+                        if (pipe[q].live) {
+                            CU(cudaGraphLaunch(sc->bounce_graph[q].exec, pipe[q].st));
+                            launches += 2 * check_every;
+                        }
+            } else {
+                for (int q = 0; q < n_pipes; q++)
+                    if (pipe[q].live) {
+                        CU(launch_wf_trace(sc->dev, rc, pipe[q].ws, b, g_n_sms, pipe[q].st));
+                        launches++;
+                    }
+                CU(mark());
+                for (int q = 0; q < n_pipes; q++)
+                    if (pipe[q].live) {
+                        CU(launch_wf_shade(sc->dev, rc, pipe[q].ws, b, g_n_sms, pipe[q].st));
+                        launches++;
+                    }
+                CU(mark());
+            }
             if ((it % check_every) == check_every - 1) {
                 // The queue lengths are read one poll late: the copy issued here is looked at only after the next
                 // check_every bounces have been enqueued, so the GPU never idles while the host waits for it. A
