@@ -26,6 +26,8 @@ constexpr size_t kMaxBatch = (size_t)1 << 30;
 bool g_profile_stages = false;
 size_t g_trace_chunk = (size_t)1 << 21; // AKB_TRACE_CHUNK: rays per staging slot of akb_trace (host batches)
 int g_check_every = 4;                 // AKB_CHECK_EVERY: bounces per graph launch / queue-length poll (even)
+int g_finish_div = 8;                  // AKB_FINISH_DIV: a pipeline whose extension queue is below slots / this is finished by wf_finish_kernel (0: never)
+int g_timeline = 0;                    // AKB_TIMELINE=1: print every poll's device time and queue lengths (tuning aid)
 int g_graphs = 1;                      // AKB_GRAPHS=0: launch every bounce's kernels one by one (tuning aid)
 int g_poll_lag = 1;                    // AKB_POLL_LAG=0: wait for every queue-length poll (tuning aid)
 int g_pipelines = 2;                   // AKB_PIPELINES: half-frame pipelines of the wavefront (1 or 2)
@@ -256,6 +258,8 @@ akb_status akb_init(int device_index) {
     if (const char *e = getenv("AKB_PIPELINES")) g_pipelines = atoi(e);
     if (const char *e = getenv("AKB_POLL_LAG")) g_poll_lag = atoi(e) != 0;
     if (const char *e = getenv("AKB_GRAPHS")) g_graphs = atoi(e) != 0;
+    if (const char *e = getenv("AKB_TIMELINE")) g_timeline = atoi(e) != 0;
+    if (const char *e = getenv("AKB_FINISH_DIV")) g_finish_div = std::max(0, atoi(e));
     if (const char *e = getenv("AKB_CHECK_EVERY")) g_check_every = std::max(2, atoi(e) & ~1);
     if (const char *e = getenv("AKB_TRACE_CHUNK")) g_trace_chunk = std::max<size_t>(1024, (size_t)atoll(e));
     if (const char *e = getenv("AKB_PIPELINE_MIN_SLOTS")) g_pipeline_min_slots = atoi(e);
@@ -365,8 +369,8 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene) {
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_fork, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_join, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&sc->cap_stream, cudaStreamNonBlocking);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_poll[0], cudaEventDisableTiming);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_poll[1], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_poll[0], g_timeline ? cudaEventDefault : cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_poll[1], g_timeline ? cudaEventDefault : cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreate(&sc->ev0);
         if (e == cudaSuccess) e = cudaEventCreate(&sc->ev1);
         if (e != cudaSuccess) st = set_err(AKB_CUDA_ERROR, "akb_scene_create: %s", cudaGetErrorString(e));
@@ -496,6 +500,7 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
         };
         CU(mark());
         const bool use_graphs = g_graphs && !g_profile_stages;
+        const int finish_div = (rc.ao || g_profile_stages) ? 0 : g_finish_div; // the AO integrator keeps to its queues
         if (use_graphs)
             for (int q = 0; q < n_pipes; q++) {
                 akb_scene::BounceGraph &g = sc->bounce_graph[q];
@@ -553,7 +558,22 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
                             CU(cudaEventSynchronize(sc->ev_poll[q]));
                         }
                         poll_pending[q] = false;
-                        if (sc->h_ctr[q].n_ext[b ^ 1] == 0 && sc->h_ctr[q].n_sh[b ^ 1] == 0) pipe[q].live = false;
+                        if (g_timeline) {
+                            float ms = 0.f;
+                            cudaEventElapsedTime(&ms, sc->ev0, sc->ev_poll[q]);
+                            fprintf(stderr, "akb timeline: pipe %d after bounce %ld: %.3f ms, n_ext %u n_sh %u\n", q, it - check_every,
+                                    ms, sc->h_ctr[q].n_ext[b ^ 1], sc->h_ctr[q].n_sh[b ^ 1]);
+                        }
+                        const uint32_t left = sc->h_ctr[q].n_ext[b ^ 1];
+                        if (left == 0 && sc->h_ctr[q].n_sh[b ^ 1] == 0) {
+                            pipe[q].live = false;
+                        } else if (finish_div > 0 && left <= (uint32_t)(pipe[q].ws.n_slots / finish_div)) {
+                            // few paths left (the count only falls from here on): one thread per path runs them out.
+                            // Everything enqueued so far ends on a shade step of parity b, so the live queues are b ^ 1.
+                            CU(launch_wf_finish(sc->dev, rc, pipe[q].ws, b ^ 1, left, pipe[q].st));
+                            launches++;
+                            pipe[q].live = false;
+                        }
                     }
                     if (pipe[q].live && g_poll_lag) {
                         CU(cudaMemcpyAsync(sc->h_ctr + q, sc->d_ctr + q, sizeof(Counters), cudaMemcpyDeviceToHost, pipe[q].st));

@@ -30,6 +30,8 @@ constexpr int kBlock = 128;
 #define AKB_SHADE_MIN_BLOCKS 6
 #endif
 constexpr uint32_t kDeadRay = 0x80000000u; // queue-entry flag: path ends at the next shade step, nothing to trace
+constexpr uint32_t kHasShadow = 0x40000000u; // queue-entry flag: the path also has an entry in the shadow queue (wf_finish_kernel)
+constexpr uint32_t kSlotMask = ~(kDeadRay | kHasShadow);
 
 __device__ __forceinline__ v3 xyz(const float4 &a) { return mk3(a.x, a.y, a.z); }
 __device__ __forceinline__ float4 mk4(v3 a, float w) { return make_float4(a.x, a.y, a.z, w); }
@@ -353,7 +355,7 @@ template <int SAMP> struct WfSrc {
     __device__ __forceinline__ bool load(uint32_t i, Trav &T, uint32_t &slot) const {
         if (i < n_ext) {
             const uint32_t e = ws.q_ext[b][i];
-            slot = e & ~kDeadRay;
+            slot = e & kSlotMask;
             if (e & kDeadRay) { // parked path: nothing to trace, the shade step just finishes it
                 T.hit.tri = -1, T.hit.mat = -1, T.any = false;
                 return false;
@@ -460,7 +462,7 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
         bool push_ext = false, push_sh = false;
         uint32_t ext_entry = 0, slot = 0;
         if (valid) {
-            slot = (rc.sort_materials ? ws.q_shade[b][k][j] : ws.q_ext[b][j]) & ~kDeadRay;
+            slot = (rc.sort_materials ? ws.q_shade[b][k][j] : ws.q_ext[b][j]) & kSlotMask;
             ext_entry = slot;
             const float4 hrec = ws.hit[slot];
             const int tri = __float_as_int(hrec.z);
@@ -527,6 +529,7 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
                 }
             }
         }
+        if (push_sh) ext_entry |= kHasShadow; // a shadow ray always comes with an extension entry (continuing or parked)
         queue_push2(push_ext, ext_entry, ws.q_ext[b ^ 1], &ctr->n_ext[b ^ 1], push_sh, slot, ws.q_sh[b ^ 1], &ctr->n_sh[b ^ 1]);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -540,6 +543,100 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
     }
     if (lane == 0 && n_done) atomicAdd(&ctr->stat_samples, (unsigned long long)n_done);
     if (lane == 0 && n_parked) atomicAdd(&ctr->stat_skipped, (unsigned long long)n_parked);
+}
+
+// Tail of a frame: once few paths are left, every further bounce costs two launches that each last as long as their
+// slowest ray, with the machine nearly empty (C3: the last 90 of 220 bounces took 12 % of the frame). This kernel is
+// launched instead, after a shade step, when the extension queue has dropped below a fraction of the slots: one thread
+// per queue entry takes over the path where the wavefront left it (pending shadow ray, parked or continuing path) and
+// runs that pixel's remaining samples to completion, in the order and arithmetic of wf_trace/wf_shade (L += shadow
+// colour before the next vertex, rays leaving a vertex at max_depth not traced, sequential film sums), so the film and
+// the ray counts do not depend on when the switch happens.
+template <int SAMP, bool TEX>
+__global__ void __launch_bounds__(kBlock) wf_finish_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
+    Counters *ctr = ws.ctr;
+    const uint32_t n = ctr->n_ext[b];
+    unsigned long long n_closest = 0, n_shadow = 0, n_samples = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t e = ws.q_ext[b][i];
+        const uint32_t slot = e & kSlotMask;
+        bool dead = (e & kDeadRay) != 0, pend = (e & kHasShadow) != 0;
+        if (dead) n_closest++; // the shade step that parked it counted it in stat_skipped; the trace launch that would balance that never runs
+        PathState<SAMP> ps;
+        ps.rng.s = ws.rng[slot];
+        ps.beta = mk3(1, 1, 1), ps.depth = 0, ps.L = mk3(0, 0, 0);
+        const float4 Lr = ws.L[slot];
+        v3 L = xyz(Lr);
+        int done = __float_as_int(Lr.w);
+        const float4 a = ws.acc[slot];
+        v3 sum = xyz(a);
+        float weight = a.w;
+        RaySeg ray, sh;
+        v3 sc = mk3(0, 0, 0);
+        ray.o = ray.d = sh.o = sh.d = mk3(0, 0, 0), ray.tmin = ray.tmax = sh.tmin = sh.tmax = 0.f;
+        if (!dead) {
+            const float4 o = ws.ray_o[slot], d = ws.ray_d[slot], bd = ws.beta[slot];
+            ray.o = xyz(o), ray.d = xyz(d), ray.tmin = o.w, ray.tmax = d.w;
+            ps.beta = xyz(bd), ps.depth = __float_as_int(bd.w);
+        }
+        if (pend) {
+            const float4 o = ws.sh_o[slot], d = ws.sh_d[slot];
+            sh.o = xyz(o), sh.d = xyz(d), sh.tmin = o.w, sh.tmax = d.w;
+            sc = xyz(ws.sh_c[slot]);
+        }
+        int x = 0, y = 0;
+        slot_to_pixel(rc.map, (int)slot + ws.slot_base, x, y);
+        for (;;) {
+            if (pend) { // wf_trace, any-hit item: unoccluded -> L += colour
+                RayHit dummy;
+                n_shadow++;
+                if (!traverse8<true>(S.nodes, S.tris, sh.o, sh.d, sh.tmin, sh.tmax, dummy)) L = add3(L, sc);
+                pend = false;
+            }
+            bool finished = true;
+            ps.L = mk3(0, 0, 0);
+            if (!dead) { // wf_trace closest-hit item + wf_shade
+                RayHit hit;
+                n_closest++;
+                if (traverse8<false>(S.nodes, S.tris, ray.o, ray.d, ray.tmin, ray.tmax, hit)) {
+                    RaySeg next;
+                    const int fl = path_vertex<SAMP>(S, ps, ray.d, hit.u, hit.v, hit.tri, rc.max_depth, rc.rr_start, next, sh, sc, TEX);
+                    bool cont = (fl & VTX_CONTINUE) != 0;
+                    pend = (fl & VTX_SHADOW) != 0;
+                    if (cont && ps.depth >= rc.max_depth && ps.depth > 0) cont = false;
+                    if (cont)
+                        ray = next, finished = false;
+                    else if (pend)
+                        dead = true, finished = false; // the film add waits for this vertex's shadow ray
+                }
+            }
+            if (finished) {
+                sum = add3(sum, clamp_sample(add3(L, ps.L), rc.ray_clamp));
+                weight += 1.0f;
+                n_samples++;
+                if (++done >= rc.spp) break;
+                float u1x, u1y, u2x, u2y; // start_sample
+                ps.rng.next2d(u2x, u2y);
+                ps.rng.next2d(u1x, u1y);
+                camera_generate_ray(S.cam, u2x, u2y, x, y, ray.o, ray.d);
+                ray.tmin = AKB_EPS, ray.tmax = INFINITY;
+                ps.beta = mk3(1, 1, 1), ps.depth = 0;
+                L = mk3(0, 0, 0);
+                dead = false;
+            }
+        }
+        ws.acc[slot] = mk4(sum, weight);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        n_closest += __shfl_down_sync(0xffffffffu, n_closest, o);
+        n_shadow += __shfl_down_sync(0xffffffffu, n_shadow, o);
+        n_samples += __shfl_down_sync(0xffffffffu, n_samples, o);
+    }
+    if ((threadIdx.x & 31) == 0 && (n_samples | n_closest | n_shadow)) {
+        atomicAdd(&ctr->stat_closest, n_closest);
+        atomicAdd(&ctr->stat_shadow, n_shadow);
+        atomicAdd(&ctr->stat_samples, n_samples);
+    }
 }
 
 __global__ void wf_resolve_kernel(RenderConfig rc, Workspace ws, float4 *__restrict__ film) {
@@ -655,6 +752,21 @@ cudaError_t launch_wf_shade(const SceneDev &S, const RenderConfig &rc, const Wor
         wf_shade_kernel<AKB_SAMPLER_LCG, true, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
     else
         wf_shade_kernel<AKB_SAMPLER_LCG, false, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wf_finish(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int parity, uint32_t n_upper,
+                             cudaStream_t st) {
+    const unsigned grid = std::max(1u, (n_upper + kBlock - 1) / kBlock);
+    const bool pcg = rc.sampler == AKB_SAMPLER_PCG, tex = S.n_textures > 0;
+    if (pcg && tex)
+        wf_finish_kernel<AKB_SAMPLER_PCG, true><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+    else if (pcg)
+        wf_finish_kernel<AKB_SAMPLER_PCG, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+    else if (tex)
+        wf_finish_kernel<AKB_SAMPLER_LCG, true><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+    else
+        wf_finish_kernel<AKB_SAMPLER_LCG, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
     return cudaGetLastError();
 }
 

@@ -64,6 +64,9 @@ cudaError_t launch_wf_trace(const SceneDev &S, const RenderConfig &rc, const Wor
                             cudaStream_t st);
 cudaError_t launch_wf_shade(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int parity, int n_sms,
                             cudaStream_t st);
+// tail of a frame: one thread per entry of q_ext[parity] runs its pixel's remaining samples to completion
+cudaError_t launch_wf_finish(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int parity, uint32_t n_upper,
+                             cudaStream_t st);
 cudaError_t launch_wf_resolve(const RenderConfig &rc, const Workspace &ws, float4 *film, cudaStream_t st);
 
 } // namespace akb
