@@ -27,6 +27,7 @@ bool g_profile_stages = false;
 size_t g_trace_chunk = (size_t)1 << 21; // AKB_TRACE_CHUNK: rays per staging slot of akb_trace (host batches)
 int g_check_every = 4;                 // AKB_CHECK_EVERY: bounces per graph launch / queue-length poll (even)
 int g_finish_div = 8;                  // AKB_FINISH_DIV: a pipeline whose extension queue is below slots / this is finished by wf_finish_kernel (0: never)
+int g_finish_max = 1 << 16;            // AKB_FINISH_MAX: ... and below this many paths (about one wave of wf_finish_kernel threads)
 int g_timeline = 0;                    // AKB_TIMELINE=1: print every poll's device time and queue lengths (tuning aid)
 int g_graphs = 1;                      // AKB_GRAPHS=0: launch every bounce's kernels one by one (tuning aid)
 int g_poll_lag = 1;                    // AKB_POLL_LAG=0: wait for every queue-length poll (tuning aid)
@@ -260,6 +261,7 @@ akb_status akb_init(int device_index) {
     if (const char *e = getenv("AKB_GRAPHS")) g_graphs = atoi(e) != 0;
     if (const char *e = getenv("AKB_TIMELINE")) g_timeline = atoi(e) != 0;
     if (const char *e = getenv("AKB_FINISH_DIV")) g_finish_div = std::max(0, atoi(e));
+    if (const char *e = getenv("AKB_FINISH_MAX")) g_finish_max = std::max(1, atoi(e));
     if (const char *e = getenv("AKB_CHECK_EVERY")) g_check_every = std::max(2, atoi(e) & ~1);
     if (const char *e = getenv("AKB_TRACE_CHUNK")) g_trace_chunk = std::max<size_t>(1024, (size_t)atoll(e));
     if (const char *e = getenv("AKB_PIPELINE_MIN_SLOTS")) g_pipeline_min_slots = atoi(e);
@@ -567,7 +569,7 @@ akb_status akb_render_device(akb_scene *sc, const akb_render_params *p, float *d
                         const uint32_t left = sc->h_ctr[q].n_ext[b ^ 1];
                         if (left == 0 && sc->h_ctr[q].n_sh[b ^ 1] == 0) {
                             pipe[q].live = false;
-                        } else if (finish_div > 0 && left <= (uint32_t)(pipe[q].ws.n_slots / finish_div)) {
+                        } else if (finish_div > 0 && left <= (uint32_t)std::min(pipe[q].ws.n_slots / finish_div, g_finish_max)) {
                             // few paths left (the count only falls from here on): one thread per path runs them out.
                             // Everything enqueued so far ends on a shade step of parity b, so the live queues are b ^ 1.
                             CU(launch_wf_finish(sc->dev, rc, pipe[q].ws, b ^ 1, left, pipe[q].st));
