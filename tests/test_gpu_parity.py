@@ -229,6 +229,44 @@ def test_wavefront_equals_megakernel_and_sorting_is_neutral():
     be.close()
 
 
+def test_finish_kernel_switch_point_is_neutral():
+    """The tail of a frame is handed to wf_finish_kernel (one thread per remaining path) once a pipeline's queue is
+    short. Wherever that happens - never, at the default point, or at the very first poll, when every path is still
+    mid-flight with shadow rays pending and parked entries in the queue - films and sample/ray counts must be the same
+    bits (AKB_FINISH_DIV / AKB_FINISH_MAX are read by akb_init)."""
+    scs = (scenes.mixed_box((80, 56), 12, 5),
+           scenes.terrain_scene(n=64, resolution=(96, 54), spp=12, max_depth=8, materials="c3", rr_start_depth=3),
+           scenes.many_light_scene(n=48, resolution=(64, 36), spp=8, max_depth=16, n_quads=500))
+    old = {k: os.environ.get(k) for k in ("AKB_FINISH_DIV", "AKB_FINISH_MAX", "AKB_PIPELINE_MIN_SLOTS")}
+    results = {}
+    try:
+        # akb_init only overrides what the environment names, so every setting is spelled out (defaults: 8, 65536, 131072)
+        for div, mx, minslots in (("0", "65536", "131072"), ("8", "65536", "131072"), ("1", "100000000", "131072"),
+                                  ("1", "100000000", "1"), ("3", "100000000", "1")):
+            os.environ.update(AKB_FINISH_DIV=div, AKB_FINISH_MAX=mx, AKB_PIPELINE_MIN_SLOTS=minslots)
+            pkg._initialised = None
+            pkg.init(0)
+            for i, sc in enumerate(scs):
+                be = backend(sc)
+                for sort in (0, 1):
+                    p = sc.integrator.params()
+                    p.mode, p.sort_materials = abi.MODE_WAVEFRONT, sort
+                    film, st = be.render(p)
+                    got = (bits(film).copy(), st.n_samples, st.n_closest_rays, st.n_shadow_rays)
+                    want = results.setdefault((i, sort), got)
+                    assert np.array_equal(got[0], want[0]) and got[1:] == want[1:], (div, mx, minslots, i, sort)
+                assert np.array_equal(results[(i, 0)][0], results[(i, 1)][0])
+                be.close()
+    finally:
+        os.environ.update(AKB_FINISH_DIV="8", AKB_FINISH_MAX="65536", AKB_PIPELINE_MIN_SLOTS="131072")
+        pkg._initialised = None
+        pkg.init(0)
+        for k, v in old.items():
+            os.environ.pop(k, None)
+            if v is not None:
+                os.environ[k] = v
+
+
 def test_extensions_vs_oracle():
     """Dielectric + Russian roulette + many lights (extensions; oracle = the extended CPU statement)."""
     for sc in (scenes.terrain_scene(n=64, resolution=(96, 54), spp=4, max_depth=8, materials="c3", rr_start_depth=3),
