@@ -26,7 +26,7 @@ constexpr size_t kMaxBatch = (size_t)1 << 30;
 bool g_profile_stages = false;
 size_t g_trace_chunk = (size_t)1 << 21; // AKB_TRACE_CHUNK: rays per staging slot of akb_trace (host batches)
 int g_check_every = 4;                 // AKB_CHECK_EVERY: bounces per graph launch / queue-length poll (even)
-int g_finish_div = 8;                  // AKB_FINISH_DIV: a pipeline whose extension queue is below slots / this is finished by wf_finish_kernel (0: never)
+int g_finish_div = 4;                  // AKB_FINISH_DIV: a pipeline whose extension queue is below slots / this is finished by wf_finish_kernel (0: never)
 int g_finish_max = 1 << 16;            // AKB_FINISH_MAX: ... and below this many paths (about one wave of wf_finish_kernel threads)
 int g_timeline = 0;                    // AKB_TIMELINE=1: print every poll's device time and queue lengths (tuning aid)
 int g_graphs = 1;                      // AKB_GRAPHS=0: launch every bounce's kernels one by one (tuning aid)

@@ -240,8 +240,8 @@ def test_finish_kernel_switch_point_is_neutral():
     old = {k: os.environ.get(k) for k in ("AKB_FINISH_DIV", "AKB_FINISH_MAX", "AKB_PIPELINE_MIN_SLOTS")}
     results = {}
     try:
-        # akb_init only overrides what the environment names, so every setting is spelled out (defaults: 8, 65536, 131072)
-        for div, mx, minslots in (("0", "65536", "131072"), ("8", "65536", "131072"), ("1", "100000000", "131072"),
+        # akb_init only overrides what the environment names, so every setting is spelled out (defaults: 4, 65536, 131072)
+        for div, mx, minslots in (("0", "65536", "131072"), ("4", "65536", "131072"), ("8", "65536", "131072"), ("1", "100000000", "131072"),
                                   ("1", "100000000", "1"), ("3", "100000000", "1")):
             os.environ.update(AKB_FINISH_DIV=div, AKB_FINISH_MAX=mx, AKB_PIPELINE_MIN_SLOTS=minslots)
             pkg._initialised = None
@@ -258,7 +258,7 @@ def test_finish_kernel_switch_point_is_neutral():
                 assert np.array_equal(results[(i, 0)][0], results[(i, 1)][0])
                 be.close()
     finally:
-        os.environ.update(AKB_FINISH_DIV="8", AKB_FINISH_MAX="65536", AKB_PIPELINE_MIN_SLOTS="131072")
+        os.environ.update(AKB_FINISH_DIV="4", AKB_FINISH_MAX="65536", AKB_PIPELINE_MIN_SLOTS="131072")
         pkg._initialised = None
         pkg.init(0)
         for k, v in old.items():
