@@ -190,7 +190,7 @@ akb_status ensure_workspace(akb_scene *sc, int n_slots) {
 #define WS(field, type)                                                                                                \
     if ((st = ws_alloc<type>(sc, n, &w.field)) != AKB_OK) return st;
     WS(ray_o, float4) WS(ray_d, float4) WS(hit, float4) WS(beta, float4) WS(L, float4) WS(rng, unsigned long long)
-    WS(sh_o, float4) WS(sh_d, float4) WS(sh_c, float4) WS(acc, float4)
+    WS(sh_o, float4) WS(sh_d, float4) WS(sh_c, float4) WS(sh_b, float4) WS(acc, float4)
     for (int b = 0; b < 2; b++) {
         WS(q_ext[b], uint32_t) WS(q_sh[b], uint32_t)
         for (int k = 0; k < kNumKeys; k++) { WS(q_shade[b][k], uint32_t) }
@@ -208,7 +208,7 @@ Workspace workspace_view(const Workspace &w, int base, int n, Counters *ctr) {
     Workspace v = w;
     v.n_slots = n, v.slot_base = w.slot_base + base, v.ctr = ctr;
     v.ray_o += base, v.ray_d += base, v.hit += base, v.beta += base, v.L += base, v.rng += base;
-    v.sh_o += base, v.sh_d += base, v.sh_c += base, v.acc += base;
+    v.sh_o += base, v.sh_d += base, v.sh_c += base, v.sh_b += base, v.acc += base;
     for (int b = 0; b < 2; b++) {
         v.q_ext[b] += base, v.q_sh[b] += base;
         for (int k = 0; k < kNumKeys; k++) v.q_shade[b][k] += base;
@@ -269,6 +269,7 @@ akb_status akb_init(int device_index) {
         int v = atoi(rb);
         if (v >= 1 && v <= 32) CU(set_refill_below(v));
     }
+    if (const char *e = getenv("AKB_NO_PARK")) CU(set_no_park(atoi(e) != 0));
     if (const char *fc = getenv("AKB_FETCH_CHUNK")) {
         int v = atoi(fc);
         if (v >= 0 && v <= 4096) CU(set_fetch_chunk(v));

@@ -82,6 +82,8 @@ __global__ void selftest_kernel(int *result, float a, float b, float c) {
 // and fetch new rays from the queue (one atomic per refill), and the warp continues with all lanes busy.
 //   Src::load(i, T, tag)  -> true: T initialised for item i; false: the item needs no traversal (result ready)
 //   Src::complete(have, i, tag, T): called by all 32 lanes together; lanes with have == true consume their result
+__constant__ int c_no_park = 1; // 0 (AKB_NO_PARK=0): a path that ends with a shadow ray pending always waits one step for it
+#define g_no_park c_no_park
 __constant__ int c_fetch_chunk = 0; // 0: reserve exactly the idle-lane count per refill; >0: warp-private chunks (AKB_FETCH_CHUNK)
 __constant__ int c_refill_below = 0; // > 0: AKB_REFILL_BELOW override; else 24 with the if-if step, 20 with the fused one (measured best on B200)
 
@@ -395,12 +397,21 @@ template <int SAMP> struct WfSrc {
                         key = type == AKB_MAT_DIFFUSE ? 1 : (type == AKB_MAT_GLOSSY ? 2 : (type == AKB_MAT_DIELECTRIC ? 3 : 0));
                     }
                 }
-            } else if (T.hit.tri < 0) { // unoccluded: L += color, kernel/pathtracer.h:156
+            } else {
                 const float4 c = ws.sh_c[slot];
-                float4 L = ws.L[slot];
-                const v3 s = add3(xyz(L), xyz(c));
-                L.x = s.x, L.y = s.y, L.z = s.z;
-                ws.L[slot] = L;
+                if (c.w != 0.f) {
+                    // last shadow ray of a sample whose pixel is already on its next one: this is the film add the
+                    // shade step would have done one bounce later ("Splat", core/film.h:66-70). The pixel's next
+                    // sample cannot finish before the next shade step, so the sums keep their order.
+                    const float4 a = ws.acc[slot];
+                    const v3 s = add3(xyz(a), T.hit.tri < 0 ? xyz(c) : xyz(ws.sh_b[slot]));
+                    ws.acc[slot] = make_float4(s.x, s.y, s.z, a.w + 1.0f);
+                } else if (T.hit.tri < 0) { // unoccluded: L += color, kernel/pathtracer.h:156
+                    float4 L = ws.L[slot];
+                    const v3 s = add3(xyz(L), xyz(c));
+                    L.x = s.x, L.y = s.y, L.z = s.z;
+                    ws.L[slot] = L;
+                }
             }
         }
         if (rc.sort_materials) { // bin closest hits by BSDF kind: one atomic per (warp, key)
@@ -506,11 +517,26 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
                     ws.rng[slot] = ps.rng.s;
                     push_ext = true, finished = false;
                 } else if (shadow) {
-                    // the film add must wait for this vertex's shadow ray: park the path for one step
-                    ws.rng[slot] = ps.rng.s;
-                    ext_entry = slot | kDeadRay;
-                    push_ext = true, finished = false;
-                    n_parked++; // the queue entry is counted by the next traversal launch but traces nothing
+                    // The path ends here, but the film add must wait for this vertex's shadow ray.
+                    const float4 Lr = ws.L[slot];
+                    const int done = __float_as_int(Lr.w) + 1;
+                    if (done < rc.spp && g_no_park) {
+                        // The pixel starts its next sample now; the traversal step that resolves the shadow ray adds
+                        // the finished sample to the film (both possible values are worked out here).
+                        ws.sh_c[slot] = mk4(clamp_sample(add3(xyz(Lr), sc), rc.ray_clamp), 1.f);
+                        ws.sh_b[slot] = mk4(clamp_sample(xyz(Lr), rc.ray_clamp), 0.f);
+                        n_done++;
+                        int x, y;
+                        slot_to_pixel(rc.map, (int)slot + ws.slot_base, x, y);
+                        start_sample<SAMP>(S, ws, (int)slot, x, y, ps.rng, done);
+                        push_ext = true, finished = false;
+                    } else {
+                        // last sample of the pixel: park the path for one step
+                        ws.rng[slot] = ps.rng.s;
+                        ext_entry = slot | kDeadRay;
+                        push_ext = true, finished = false;
+                        n_parked++; // the queue entry is counted by the next traversal launch but traces nothing
+                    }
                 }
             }
             if (finished) { // "Splat" + regenerate (gpu/cuda/integrator.cpp:385-401, core/film.h:66-70)
@@ -579,10 +605,13 @@ __global__ void __launch_bounds__(kBlock) wf_finish_kernel(SceneDev S, RenderCon
             ray.o = xyz(o), ray.d = xyz(d), ray.tmin = o.w, ray.tmax = d.w;
             ps.beta = xyz(bd), ps.depth = __float_as_int(bd.w);
         }
+        bool last_of_sample = false; // the pending shadow ray decides an already finished sample's film value
+        v3 sb = mk3(0, 0, 0);
         if (pend) {
-            const float4 o = ws.sh_o[slot], d = ws.sh_d[slot];
+            const float4 o = ws.sh_o[slot], d = ws.sh_d[slot], c = ws.sh_c[slot];
             sh.o = xyz(o), sh.d = xyz(d), sh.tmin = o.w, sh.tmax = d.w;
-            sc = xyz(ws.sh_c[slot]);
+            sc = xyz(c);
+            if (c.w != 0.f) last_of_sample = true, sb = xyz(ws.sh_b[slot]);
         }
         int x = 0, y = 0;
         slot_to_pixel(rc.map, (int)slot + ws.slot_base, x, y);
@@ -590,7 +619,11 @@ __global__ void __launch_bounds__(kBlock) wf_finish_kernel(SceneDev S, RenderCon
             if (pend) { // wf_trace, any-hit item: unoccluded -> L += colour
                 RayHit dummy;
                 n_shadow++;
-                if (!traverse8<true>(S.nodes, S.tris, sh.o, sh.d, sh.tmin, sh.tmax, dummy)) L = add3(L, sc);
+                const bool unoccluded = !traverse8<true>(S.nodes, S.tris, sh.o, sh.d, sh.tmin, sh.tmax, dummy);
+                if (last_of_sample) // wf_trace's film add; the sample itself was counted by the shade step
+                    sum = add3(sum, unoccluded ? sc : sb), weight += 1.0f, last_of_sample = false;
+                else if (unoccluded)
+                    L = add3(L, sc);
                 pend = false;
             }
             bool finished = true;
@@ -654,6 +687,7 @@ template <class K> int blocks_per_sm(K kernel, int block) {
 } // namespace
 
 cudaError_t set_refill_below(int v) { return cudaMemcpyToSymbol(c_refill_below, &v, sizeof(int)); }
+cudaError_t set_no_park(int v) { return cudaMemcpyToSymbol(c_no_park, &v, sizeof(int)); }
 cudaError_t set_fetch_chunk(int v) { return cudaMemcpyToSymbol(c_fetch_chunk, &v, sizeof(int)); }
 
 cudaError_t launch_selftest(int *d_result, cudaStream_t st) {

@@ -28,7 +28,9 @@ struct Workspace {
     float4 *beta;               // (beta | depth bits)
     float4 *L;                  // (L | samples-done bits)
     unsigned long long *rng;    // sampler state
-    float4 *sh_o, *sh_d, *sh_c; // shadow ray + the radiance it carries
+    float4 *sh_o, *sh_d, *sh_c; // shadow ray + the radiance it carries (w = 0), or, for the last shadow ray of a sample
+                                // whose pixel has already started its next one (w = 1): the sample's film value if it is
+    float4 *sh_b;               // unoccluded (sh_c) and if it is occluded (sh_b)
     float4 *acc;                // per-slot film accumulator (sum L | sum weight): Tile::add_sample
     uint32_t *q_ext[2], *q_sh[2], *q_shade[2][kNumKeys];
     Counters *ctr;
@@ -50,6 +52,7 @@ struct LaunchDims {
 cudaError_t launch_selftest(int *d_result, cudaStream_t st);
 cudaError_t set_refill_below(int v);
 cudaError_t set_fetch_chunk(int v);
+cudaError_t set_no_park(int v);
 cudaError_t launch_trace_batch(const SceneDev &S, const float4 *org, const float4 *dir, size_t n, int any_hit,
                                akb_hit *hits, int32_t *occ, uint32_t *fetch_cursor, int n_sms, cudaStream_t st);
 cudaError_t launch_generate_rays(const SceneDev &S, const int32_t *xy, const float *u2, size_t n, float4 *org,

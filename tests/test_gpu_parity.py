@@ -229,21 +229,26 @@ def test_wavefront_equals_megakernel_and_sorting_is_neutral():
     be.close()
 
 
-def test_finish_kernel_switch_point_is_neutral():
-    """The tail of a frame is handed to wf_finish_kernel (one thread per remaining path) once a pipeline's queue is
-    short. Wherever that happens - never, at the default point, or at the very first poll, when every path is still
-    mid-flight with shadow rays pending and parked entries in the queue - films and sample/ray counts must be the same
-    bits (AKB_FINISH_DIV / AKB_FINISH_MAX are read by akb_init)."""
+def test_finish_kernel_switch_point_and_parking_are_neutral():
+    """Two scheduling choices of the wavefront that must not show in the results. (1) The tail of a frame is handed to
+    wf_finish_kernel (one thread per remaining path) once a pipeline's queue is short: never, at the default point, or
+    at the very first poll, when every path is still mid-flight with shadow rays pending and parked entries in the
+    queue. (2) A path that ends with a shadow ray pending either waits one bounce for it (AKB_NO_PARK=0) or lets the
+    traversal step add the finished sample to the film while the pixel already runs its next sample. Films and
+    sample/ray counts must be the same bits throughout (the switches are read by akb_init)."""
     scs = (scenes.mixed_box((80, 56), 12, 5),
            scenes.terrain_scene(n=64, resolution=(96, 54), spp=12, max_depth=8, materials="c3", rr_start_depth=3),
            scenes.many_light_scene(n=48, resolution=(64, 36), spp=8, max_depth=16, n_quads=500))
-    old = {k: os.environ.get(k) for k in ("AKB_FINISH_DIV", "AKB_FINISH_MAX", "AKB_PIPELINE_MIN_SLOTS")}
+    keys = ("AKB_FINISH_DIV", "AKB_FINISH_MAX", "AKB_PIPELINE_MIN_SLOTS", "AKB_NO_PARK")
+    default = ("4", "65536", "131072", "1")
+    old = {k: os.environ.get(k) for k in keys}
     results = {}
     try:
-        # akb_init only overrides what the environment names, so every setting is spelled out (defaults: 4, 65536, 131072)
-        for div, mx, minslots in (("0", "65536", "131072"), ("4", "65536", "131072"), ("8", "65536", "131072"), ("1", "100000000", "131072"),
-                                  ("1", "100000000", "1"), ("3", "100000000", "1")):
-            os.environ.update(AKB_FINISH_DIV=div, AKB_FINISH_MAX=mx, AKB_PIPELINE_MIN_SLOTS=minslots)
+        # akb_init only overrides what the environment names, so every setting is spelled out
+        for cfg in (("0", "65536", "131072", "0"), ("0", "65536", "131072", "1"), default, ("8", "65536", "131072", "0"),
+                    ("1", "100000000", "131072", "1"), ("1", "100000000", "1", "1"), ("1", "100000000", "1", "0"),
+                    ("3", "100000000", "1", "1")):
+            os.environ.update(dict(zip(keys, cfg)))
             pkg._initialised = None
             pkg.init(0)
             for i, sc in enumerate(scs):
@@ -254,11 +259,11 @@ def test_finish_kernel_switch_point_is_neutral():
                     film, st = be.render(p)
                     got = (bits(film).copy(), st.n_samples, st.n_closest_rays, st.n_shadow_rays)
                     want = results.setdefault((i, sort), got)
-                    assert np.array_equal(got[0], want[0]) and got[1:] == want[1:], (div, mx, minslots, i, sort)
+                    assert np.array_equal(got[0], want[0]) and got[1:] == want[1:], (cfg, i, sort)
                 assert np.array_equal(results[(i, 0)][0], results[(i, 1)][0])
                 be.close()
     finally:
-        os.environ.update(AKB_FINISH_DIV="4", AKB_FINISH_MAX="65536", AKB_PIPELINE_MIN_SLOTS="131072")
+        os.environ.update(dict(zip(keys, default)))
         pkg._initialised = None
         pkg.init(0)
         for k, v in old.items():
