@@ -336,7 +336,7 @@ def main():
                 "config": {"workload": name, "mode": a.mode,
                            "parallelism": ("%s-split x%d, scene replicated, one NCCL sum-reduce of the film per frame" % (split, world))
                            if world > 1 else "single", "tile": 32, "l2": "inputs larger than L2: BVH+triangles %.0f MB, shading records %.0f MB, path state %.0f MB"
-                           % ((info["bvh_bytes"] + info["triangle_bytes"]) / 1e6, info["n_triangles"] * 96 / 1e6, W * H * 208 / 1e6),
+                           % ((info["bvh_bytes"] + info["triangle_bytes"]) / 1e6, info["n_triangles"] * 96 / 1e6, W * H * 224 / 1e6),
                            "bvh_nodes": info["n_bvh_nodes"], "scene_build_s": round(build_s, 2),
                            "bvh_build": {1: "host SAH", 2: "device PLOC"}.get(info["bvh_build"]), "bvh_build_s": round(info["build_us"] / 1e6, 3)},
                 "clocks": clk,
