@@ -96,7 +96,9 @@ class ClockSampler:
 
 
 def cpu_reference_run(pkg, workload, spp, rows, steps=1, warmup=0):
-    """Times the reference's CPU path tracer (own BVH, all host threads) on `rows` image rows of the workload."""
+    """Times the reference's CPU path tracer (own BVH, all host threads) on `rows` image rows of the workload: bands of
+    rows spread evenly over the frame, ALL bands handed over in one call, which schedules them the way the reference
+    does (16x16-pixel tiles, one shared work list, kernel/integrators/cpu/integrator.cpp:115-141)."""
     from oracle_libs import Oracle, Reference, have_ref
     sc, name = make_scene(pkg, workload, spp, ref_subset=True)
     W, H = sc.camera.resolution
@@ -107,29 +109,32 @@ def cpu_reference_run(pkg, workload, spp, rows, steps=1, warmup=0):
     else:
         impl, kind = Oracle(sc), "port"
     build_s = time.time() - t0
-    # bands of rows spread evenly over the frame: an unbiased sample of sky, horizon and terrain pixels
+    # bands spread evenly over the frame: an unbiased sample of sky, horizon and terrain pixels
     # (one contiguous band would be all terrain, all sky - or, for C4, the void between the placed copies)
-    band = 4 if rows >= 8 else 1  # a few rows per call keep the harness's per-call cost (~3 ms) in the noise
+    band = 8 if rows >= 16 else 1
     nb = max(1, rows // band)
     rows = nb * band
     ys = [min(H - band, int((i + 0.5) * H / nb)) for i in range(nb)]
     rects = [(0, y, W, y + band) for y in ys]
     p = sc.integrator.params()
-    cores = os.cpu_count()
-    times = []
+    threads = os.cpu_count()
+    times, busy = [], []
     for i in range(warmup + steps):
         t = time.perf_counter()
-        for rect in rects:
-            impl.render(p, rect=rect, threads=cores)
+        impl.render_rects(p, rects, threads=threads)
         if i >= warmup:
             times.append(time.perf_counter() - t)
+            busy.append(impl.busy[0] / max(impl.busy[1], 1e-9))
     n_samples = W * rows * sc.integrator.spp
     sec = float(np.mean(times))
-    sample = ("%s; CPU sample = %d bands of %d image rows spread evenly over the frame (first rows y = %d, %d, ... %d; %d x %d px x %d spp = %d samples per step)%s; BVH build %.1f s not included"
-              % (name, nb, band, ys[0], ys[1] if nb > 1 else ys[0], ys[-1], W, rows, sc.integrator.spp, n_samples,
-                 "; reference has no Dielectric BSDF: those 10% of triangles are shaded as Diffuse" if workload == "c3" else "",
+    threads_busy = float(np.mean(busy))
+    sample = ("%s; CPU sample = %d bands of %d image rows spread evenly over the frame (first rows y = %d, %d, ... %d; %d x %d px x %d spp = %d samples per step), one call, 16x16-pixel tiles over %d worker threads, %.1f of them busy on average (thread CPU time / wall)%s; BVH build %.1f s not included"
+              % (name, nb, band, ys[0], ys[1] if nb > 1 else ys[0], ys[-1], W, rows, sc.integrator.spp, n_samples, threads, threads_busy,
+                 "; reference has no Dielectric BSDF: those 10% of triangles are shaded as Diffuse" if workload == "c3" else
+                 ("; reference has no Russian roulette: run without it" if workload == "c5" else ""),
                  build_s))
-    return {"value": n_samples / sec / 1e6, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": sample, "workload": name,
+    return {"value": n_samples / sec / 1e6, "unit": "Msamples/s", "cores": int(round(threads_busy)), "threads": threads,
+            "threads_busy": threads_busy, "kind": kind, "sample": sample, "workload": name,
             "seconds_per_step": sec, "samples_per_step": n_samples}
 
 
@@ -147,7 +152,7 @@ def main():
                     help="akb_bvh_build: library default (host SAH below 4 Mi triangles, device PLOC above), or force one")
     ap.add_argument("--spp", type=int, default=0)
     ap.add_argument("--mode", default="wavefront", choices=["wavefront", "megakernel"])
-    ap.add_argument("--cpu-rows", type=int, default=24)
+    ap.add_argument("--cpu-rows", type=int, default=96)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     a = ap.parse_args()
@@ -170,7 +175,8 @@ def main():
                 "steps": a.steps, "warmup": a.warmup, "ms_per_step": r["seconds_per_step"] * 1e3, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": r["workload"], "mode": "reference CPU path (own BVH), bounded sample: see cpu_baseline.sample"},
-                "cpu_baseline": {"value": r["value"], "unit": "Msamples/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
+                "cpu_baseline": {"value": r["value"], "unit": "Msamples/s", "cores": r["cores"], "threads": r["threads"],
+                                 "threads_busy": r["threads_busy"], "kind": r["kind"], "sample": r["sample"]},
                 "e2e": {"value": r["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
         emit(line)
@@ -327,7 +333,7 @@ def main():
         if not a.no_cpu_baseline and world == 1:
             try:
                 cpu = cpu_reference_run(pkg, a.workload, a.spp, a.cpu_rows)
-                cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+                cpu = {k: cpu[k] for k in ("value", "unit", "cores", "threads", "threads_busy", "kind", "sample")}
             except Exception as ex:  # the checker is optional for the product; report why
                 cpu = {"value": None, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: %r" % (ex,)}
         line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": a.steps,

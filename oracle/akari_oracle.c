@@ -21,11 +21,13 @@
  * and (ii) where the reference's unpadded slab test (kernel/bvh-accelerator.h:89-103) culls a box whose
  * triangle the ray does hit (a reference false-miss).
  */
+#define _POSIX_C_SOURCE 200809L
 #include <math.h>
 #include <pthread.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 #include "../include/akari_b200.h"
 
@@ -745,9 +747,15 @@ typedef struct job {
     /* trace */
     const float *org, *dir; size_t n; int any_hit; akb_hit *hits; int32_t *occ;
     /* render */
-    const akb_render_params *p; int x0, y0, x1, y1; float *out; uint64_t counts[3];
+    const akb_render_params *p; const int32_t *tiles; long n_tiles; float *out; uint64_t counts[3];
+    long long cpu_ns; /* CPU time summed over the workers (CLOCK_THREAD_CPUTIME_ID) */
     volatile long next; pthread_mutex_t mu;
 } job_t;
+
+static long long thread_cpu_ns(void) {
+    struct timespec ts; clock_gettime(CLOCK_THREAD_CPUTIME_ID, &ts);
+    return (long long)ts.tv_sec * 1000000000ll + ts.tv_nsec;
+}
 
 static long job_fetch(job_t *j, long step) { return __sync_fetch_and_add(&j->next, step); }
 
@@ -772,18 +780,22 @@ static void *trace_worker(void *arg) {
     return NULL;
 }
 
-/* cpu::PathTracer::render's per-pixel loop (kernel/integrators/cpu/integrator.cpp:121-135) + Tile::add_sample /
- * Film::merge_tile (core/film.h:66-95). ray_clamp > 0 applies the GPU integrator's per-sample clamp
+/* cpu::PathTracer::render's tile + per-pixel loop (kernel/integrators/cpu/integrator.cpp:115-135) + Tile::add_sample /
+ * Film::merge_tile (core/film.h:66-95). Work items are 16x16-pixel tiles (the reference's tile_size) drained by all
+ * workers through one counter (core/parallel.cpp:119-129). ray_clamp > 0 applies the GPU integrator's per-sample clamp
  * (gpu/cuda/integrator.cpp:196-198: clamp_zero then min(L, ray_clamp)). */
 static void *render_worker(void *arg) {
     job_t *j = (job_t *)arg;
     const akb_render_params *p = j->p;
     const int W = j->s->cam.w;
     uint64_t c0 = 0, c1 = 0, c2 = 0;
+    const long long t_start = thread_cpu_ns();
     for (;;) {
-        long y = job_fetch(j, 1);
-        if (y >= j->y1) break;
-        for (int x = j->x0; x < j->x1; x++) {
+        const long k = job_fetch(j, 1);
+        if (k >= j->n_tiles) break;
+        const int32_t *tj = j->tiles + 4 * k;
+        for (int y = tj[1]; y < tj[3]; y++)
+        for (int x = tj[0]; x < tj[2]; x++) {
             sampler_t smp; memset(&smp, 0, sizeof smp); smp.kind = p->sampler;
             /* AKB_SPLIT_SAMPLE (include/akari_b200.h): this rank's share of the samples, per-rank seed offset */
             const int world = p->world_size > 0 ? p->world_size : 1;
@@ -817,6 +829,7 @@ static void *render_worker(void *arg) {
     }
     pthread_mutex_lock(&j->mu);
     j->counts[0] += c0; j->counts[1] += c1; j->counts[2] += c2;
+    j->cpu_ns += thread_cpu_ns() - t_start;
     pthread_mutex_unlock(&j->mu);
     return NULL;
 }
@@ -840,15 +853,42 @@ int akor_trace(const oracle_scene *s, const float *org_tmin, const float *dir_tm
     return 0;
 }
 
-/* counts (may be NULL): [0] samples, [1] closest-hit rays, [2] shadow rays */
+/* Renders the pixel rectangles rects[4*r..] = (x0, y0, x1, y1). counts (may be NULL): [0] samples, [1] closest-hit
+ * rays, [2] shadow rays. busy (may be NULL): [0] CPU seconds summed over the workers, [1] wall seconds. */
+int akor_render_rects(const oracle_scene *s, const akb_render_params *p, const int32_t *rects, int n_rects, float *out_rgbw,
+                      int n_threads, uint64_t *counts, double *busy) {
+    if (p->integrator != AKB_INTEGRATOR_PATH && p->integrator != AKB_INTEGRATOR_AO) return 1;
+    const int T = 16;
+    long n_tiles = 0;
+    for (int r = 0; r < n_rects; r++) {
+        const long w = rects[4 * r + 2] - rects[4 * r], h = rects[4 * r + 3] - rects[4 * r + 1];
+        if (w > 0 && h > 0) n_tiles += ((w + T - 1) / T) * ((h + T - 1) / T);
+    }
+    int32_t *tiles = (int32_t *)malloc(sizeof(int32_t) * 4 * (size_t)(n_tiles > 0 ? n_tiles : 1));
+    long k = 0;
+    for (int r = 0; r < n_rects; r++)
+        for (int ty = rects[4 * r + 1]; ty < rects[4 * r + 3]; ty += T)
+            for (int tx = rects[4 * r]; tx < rects[4 * r + 2]; tx += T) {
+                tiles[4 * k] = tx; tiles[4 * k + 1] = ty;
+                tiles[4 * k + 2] = tx + T < rects[4 * r + 2] ? tx + T : rects[4 * r + 2];
+                tiles[4 * k + 3] = ty + T < rects[4 * r + 3] ? ty + T : rects[4 * r + 3];
+                k++;
+            }
+    job_t j; memset(&j, 0, sizeof j);
+    j.s = s; j.p = p; j.tiles = tiles; j.n_tiles = n_tiles; j.out = out_rgbw; j.next = 0;
+    struct timespec w0, w1; clock_gettime(CLOCK_MONOTONIC, &w0);
+    run_threads(render_worker, &j, n_threads);
+    clock_gettime(CLOCK_MONOTONIC, &w1);
+    free(tiles);
+    if (counts) { counts[0] = j.counts[0]; counts[1] = j.counts[1]; counts[2] = j.counts[2]; }
+    if (busy) { busy[0] = (double)j.cpu_ns * 1e-9; busy[1] = (double)(w1.tv_sec - w0.tv_sec) + 1e-9 * (double)(w1.tv_nsec - w0.tv_nsec); }
+    return 0;
+}
+
 int akor_render(const oracle_scene *s, const akb_render_params *p, int x0, int y0, int x1, int y1, float *out_rgbw,
                 int n_threads, uint64_t *counts) {
-    if (p->integrator != AKB_INTEGRATOR_PATH && p->integrator != AKB_INTEGRATOR_AO) return 1;
-    job_t j; memset(&j, 0, sizeof j);
-    j.s = s; j.p = p; j.x0 = x0; j.y0 = y0; j.x1 = x1; j.y1 = y1; j.out = out_rgbw; j.next = y0;
-    run_threads(render_worker, &j, n_threads);
-    if (counts) { counts[0] = j.counts[0]; counts[1] = j.counts[1]; counts[2] = j.counts[2]; }
-    return 0;
+    const int32_t rect[4] = {x0, y0, x1, y1};
+    return akor_render_rects(s, p, rect, 1, out_rgbw, n_threads, counts, NULL);
 }
 
 int akor_generate_rays(const oracle_scene *s, const int32_t *xy, const float *u2, size_t n, float *org_tmin,

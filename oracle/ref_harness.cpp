@@ -18,6 +18,7 @@
 #include <akari/core/device.h>
 
 #include <atomic>
+#include <ctime>
 #include <cstring>
 #include <memory>
 #include <thread>
@@ -272,11 +273,16 @@ int akref_sampler_kat(int sampler_kind, uint64_t seed, int n, float *out, float 
     return 0;
 }
 
-// The sampling loop of cpu::PathTracer::render (kernel/integrators/cpu/integrator.cpp:115-135) over the pixel
-// rectangle [x0,x1) x [y0,y1), writing (sum L, sum weight) per pixel as float4 into out_rgbw[(y*W+x)*4].
-// Pixels outside the rectangle are left untouched. counts (may be NULL): [0] samples.
-int akref_render(void *h, const akb_render_params *p, int x0, int y0, int x1, int y1, float *out_rgbw,
-                 int n_threads) {
+// The sampling loop of cpu::PathTracer::render (kernel/integrators/cpu/integrator.cpp:115-135) over a list of pixel
+// rectangles [x0,x1) x [y0,y1) (rects = 4 ints each), writing (sum L, sum weight) per pixel as float4 into
+// out_rgbw[(y*W+x)*4]. Pixels outside the rectangles are left untouched.
+// Scheduling is the reference's: the rectangles are cut into 16x16-pixel tiles (tile_size, cpu/integrator.cpp:92,
+// clipped to their rectangle) and ALL tiles of ALL rectangles form one work list that n_threads workers drain through
+// one shared counter (core/parallel.cpp:119-129, parallel_for_2d over the tile grid) - so a call with a few thin bands
+// still keeps every host thread busy. busy (may be NULL): [0] = CPU seconds summed over the workers
+// (CLOCK_THREAD_CPUTIME_ID), [1] = wall seconds of the parallel region; [0]/[1] = threads actually busy.
+int akref_render_rects(void *h, const akb_render_params *p, const int32_t *rects, int n_rects, float *out_rgbw,
+                       int n_threads, double *busy) {
     AKR_IMPORT_TYPES()
     auto *rs = (RefScene *)h;
     const bool ao = p->integrator == AKB_INTEGRATOR_AO;
@@ -312,48 +318,82 @@ int akref_render(void *h, const akb_render_params *p, int x0, int y0, int x1, in
     if (n_threads <= 0)
         n_threads = (int)std::thread::hardware_concurrency();
     const int spp = p->spp, max_depth = p->max_depth;
-    std::atomic<int> next_row{y0};
+    struct TileJob {
+        int x0, y0, x1, y1;
+    };
+    std::vector<TileJob> tiles;
+    const int T = 16;
+    for (int r = 0; r < n_rects; r++) {
+        const int rx0 = rects[4 * r], ry0 = rects[4 * r + 1], rx1 = rects[4 * r + 2], ry1 = rects[4 * r + 3];
+        for (int ty = ry0; ty < ry1; ty += T)
+            for (int tx = rx0; tx < rx1; tx += T)
+                tiles.push_back(TileJob{tx, ty, std::min(tx + T, rx1), std::min(ty + T, ry1)});
+    }
+    std::atomic<size_t> next_tile{0};
+    std::atomic<long long> cpu_ns{0};
+    auto thread_ns = []() {
+        timespec ts;
+        clock_gettime(CLOCK_THREAD_CPUTIME_ID, &ts);
+        return (long long)ts.tv_sec * 1000000000ll + ts.tv_nsec;
+    };
     auto work = [&]() {
+        const long long t0 = thread_ns();
         auto &camera = scene.camera;
         auto sampler = scene.sampler;
         for (;;) {
-            int y = next_row.fetch_add(1);
-            if (y >= y1)
+            const size_t k = next_tile.fetch_add(1);
+            if (k >= tiles.size())
                 break;
-            for (int x = x0; x < x1; x++) {
-                sampler.set_sample_index(x + y * W);
-                Spectrum sum(0);
-                Float weight = 0;
-                for (int s = 0; s < spp; s++) {
-                    sampler.start_next_sample();
-                    if (ao) { // cpu/integrator.cpp:72-80
-                        CameraSample<C> sample = camera.generate_ray(sampler.next2d(), sampler.next2d(), int2(x, y));
-                        auto L = ao_li(sample.ray, sampler);
-                        weight += 1.0f;
-                        sum += L;
-                        continue;
+            const TileJob tj = tiles[k];
+            for (int y = tj.y0; y < tj.y1; y++)
+                for (int x = tj.x0; x < tj.x1; x++) {
+                    sampler.set_sample_index(x + y * W);
+                    Spectrum sum(0);
+                    Float weight = 0;
+                    for (int s = 0; s < spp; s++) {
+                        sampler.start_next_sample();
+                        if (ao) { // cpu/integrator.cpp:72-80
+                            CameraSample<C> sample = camera.generate_ray(sampler.next2d(), sampler.next2d(), int2(x, y));
+                            auto L = ao_li(sample.ray, sampler);
+                            weight += 1.0f;
+                            sum += L;
+                            continue;
+                        }
+                        GenericPathTracer<C> pt;
+                        pt.depth = 0;
+                        pt.max_depth = max_depth;
+                        pt.sampler = sampler;
+                        pt.run_megakernel(scene, camera, int2(x, y));
+                        sampler = pt.sampler;
+                        weight += 1.0f; // Tile::add_sample, core/film.h:66-70
+                        sum += pt.L;
                     }
-                    GenericPathTracer<C> pt;
-                    pt.depth = 0;
-                    pt.max_depth = max_depth;
-                    pt.sampler = sampler;
-                    pt.run_megakernel(scene, camera, int2(x, y));
-                    sampler = pt.sampler;
-                    weight += 1.0f;   // Tile::add_sample, core/film.h:66-70
-                    sum += pt.L;
+                    float *o = out_rgbw + 4 * ((size_t)y * W + x);
+                    o[0] = sum[0], o[1] = sum[1], o[2] = sum[2], o[3] = weight;
                 }
-                float *o = out_rgbw + 4 * ((size_t)y * W + x);
-                o[0] = sum[0], o[1] = sum[1], o[2] = sum[2], o[3] = weight;
-            }
         }
+        cpu_ns += thread_ns() - t0;
     };
+    timespec w0, w1;
+    clock_gettime(CLOCK_MONOTONIC, &w0);
     std::vector<std::thread> ts;
     for (int t = 1; t < n_threads; t++)
         ts.emplace_back(work);
     work();
     for (auto &t : ts)
         t.join();
+    clock_gettime(CLOCK_MONOTONIC, &w1);
+    if (busy) {
+        busy[0] = (double)cpu_ns.load() * 1e-9;
+        busy[1] = (double)(w1.tv_sec - w0.tv_sec) + 1e-9 * (double)(w1.tv_nsec - w0.tv_nsec);
+    }
     return 0;
+}
+
+int akref_render(void *h, const akb_render_params *p, int x0, int y0, int x1, int y1, float *out_rgbw,
+                 int n_threads) {
+    const int32_t rect[4] = {x0, y0, x1, y1};
+    return akref_render_rects(h, p, rect, 1, out_rgbw, n_threads, nullptr);
 }
 
 } // extern "C"

@@ -115,6 +115,20 @@ class Oracle(_Base):
         self.counts = tuple(int(c) for c in counts)
         return film
 
+    def render_rects(self, params, rects, threads=0):
+        """All rectangles in ONE call (one work list of 16x16 tiles over every host thread); sets self.busy =
+        (CPU seconds summed over the workers, wall seconds)."""
+        film = np.zeros((self.height, self.width, 4), np.float32)
+        r = np.ascontiguousarray(rects, np.int32).reshape(-1, 4)
+        counts = (C.c_uint64 * 3)()
+        busy = (C.c_double * 2)()
+        rc = self.lib.akor_render_rects(self.h, C.byref(params), _ptr(r), C.c_int(r.shape[0]), _ptr(film),
+                                        C.c_int(threads or os.cpu_count()), counts, busy)
+        assert rc == 0
+        self.counts = tuple(int(c) for c in counts)
+        self.busy = (float(busy[0]), float(busy[1]))
+        return film
+
     def film_to_srgb8(self, film):
         h, w = film.shape[:2]
         out = np.zeros((h, w, 3), np.uint8)
@@ -134,6 +148,19 @@ class Reference(_Base):
         rc = self.lib.akref_render(self.h, C.byref(params), x0, y0, x1, y1, _ptr(film),
                                    C.c_int(threads or os.cpu_count()))
         assert rc == 0
+        return film
+
+
+    def render_rects(self, params, rects, threads=0):
+        """All rectangles in ONE call: the reference's scheduling (16x16 tiles, one shared work list, all host threads);
+        sets self.busy = (CPU seconds summed over the workers, wall seconds)."""
+        film = np.zeros((self.height, self.width, 4), np.float32)
+        r = np.ascontiguousarray(rects, np.int32).reshape(-1, 4)
+        busy = (C.c_double * 2)()
+        rc = self.lib.akref_render_rects(self.h, C.byref(params), _ptr(r), C.c_int(r.shape[0]), _ptr(film),
+                                         C.c_int(threads or os.cpu_count()), busy)
+        assert rc == 0
+        self.busy = (float(busy[0]), float(busy[1]))
         return film
 
 
