@@ -100,6 +100,41 @@ def instanced_scene(n=708, resolution=(3840, 2160), spp=256, max_depth=8, copies
     return Scene(cam, Path(spp=spp, max_depth=max_depth, ray_clamp=0.0, **path_kw), shapes)
 
 
+def multi_mesh_scene(n=20, resolution=(64, 36), spp=4, max_depth=5, coincident=False, **path_kw):
+    """C4 in miniature, for parity tests of the two-level wrapper (kernel/bvh-accelerator.h:651-678: geom_id = mesh
+    index, prim_id = index inside the mesh, candidates of different meshes resolved by `localHit.t < record.t`):
+    2 x 2 placed copies of a small M1 at a pitch of 90 units, so that neighbouring copies OVERLAP in 10-unit strips and
+    rays cross from one mesh into the next; every mesh has its own material table in a different order (the per-mesh
+    material remap). coincident=True puts the fourth mesh exactly on top of mesh 0 (the same triangles, so every hit on
+    either is an exact-t tie between two meshes) plus one small triangle below the terrain.
+    The scene stays at FOUR meshes on purpose: from five meshes on the reference's own TLAS loses meshes (measured with
+    oracle/_ref: 5x1, 3x2 and 5x2 placed copies are only ever hit on their last one or two meshes;
+    BVHHandleConstructor, kernel/bvh-accelerator.h:643-648, stores the address of a constructor argument in every
+    handle - a dangling pointer once the constructor returns), which is not behaviour to pin."""
+    verts, tris, n_terrain = terrain_arrays(n)
+    palette = [DiffuseMaterial((0.7, 0.6, 0.5)), GlossyMaterial((0.8, 0.8, 0.8), 0.3), DiffuseMaterial((0.2, 0.5, 0.8)),
+               EmissiveMaterial((40.0,) * 3)]
+    rng = np.random.default_rng(77)
+    kind = rng.integers(0, 3, n_terrain)  # which palette entry a terrain triangle uses (3 = the light)
+    kind = np.concatenate([kind, np.full(tris.shape[0] - n_terrain, 3)])
+    shapes = []
+    offs = [np.array([(ix - 0.5) * 90.0, 0.0, (iz - 0.5) * 90.0], F32) for ix in range(2) for iz in range(2)]
+    if coincident:
+        offs[3] = offs[0]
+    for k, off in enumerate(offs):
+        order = np.roll(np.arange(4), k)  # mesh k's table: palette[order[j]] at local index j
+        local = np.argsort(order)         # palette entry -> local index
+        v, t, mi = verts + off, tris, local[kind].astype(np.int32)
+        if coincident and k == 3:
+            extra = np.array([[0, -20, 0], [1, -20, 0], [0, -20, 1]], F32) + off
+            t = np.concatenate([t, np.array([[v.shape[0], v.shape[0] + 1, v.shape[0] + 2]], np.int32)])
+            v = np.concatenate([v, extra])
+            mi = np.concatenate([mi, local[:1].astype(np.int32)])
+        shapes.append(AkariMesh(materials=[palette[i] for i in order], vertices=v, indices=t, material_indices=mi))
+    cam = PerspectiveCamera(fov=60, position=(0, 60, 150), rotation=(0, -25, 0), resolution=resolution)
+    return Scene(cam, Path(spp=spp, max_depth=max_depth, ray_clamp=0.0, **path_kw), shapes)
+
+
 def many_light_scene(n=708, resolution=(1920, 1080), spp=128, max_depth=16, n_quads=5000, rr_start_depth=3, seed=1234,
                      **path_kw):
     """C5: all-Diffuse M1 + n_quads emissive 0.5x0.5 quads on a 100x50 lattice at y = 25 + U(0,3), facing -y,

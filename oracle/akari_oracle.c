@@ -526,6 +526,17 @@ typedef struct { v3 L, beta; int depth, max_depth; sampler_t smp; uint64_t n_clo
 
 static inline int is_black(v3 c) { return !((c.x > 0.0f) || (c.y > 0.0f) || (c.z > 0.0f)); }
 
+/* Optional per-thread log of the rays a path traces (akor_pixel_rays: diagnosis of single-pixel differences).
+ * 9 floats per ray: kind (0 closest, 1 any hit), o, d, tmin, tmax. */
+static __thread float *g_raylog = NULL;
+static __thread int g_raylog_n = 0, g_raylog_cap = 0;
+static void log_ray(int kind, const ray_t *r) {
+    if (!g_raylog || g_raylog_n >= g_raylog_cap) return;
+    float *o = g_raylog + 9 * g_raylog_n++;
+    o[0] = (float)kind; o[1] = r->o.x; o[2] = r->o.y; o[3] = r->o.z; o[4] = r->d.x; o[5] = r->d.y; o[6] = r->d.z;
+    o[7] = r->tmin; o[8] = r->tmax;
+}
+
 /* GenericPathTracer::run_megakernel (kernel/pathtracer.h:61-163) + extensions (rr_start_depth, dielectric). */
 static void run_path(const oracle_scene *s, path_t *pt, int px, int py, int rr_start) {
     float u1x, u1y, u2x, u2y;
@@ -536,6 +547,7 @@ static void run_path(const oracle_scene *s, path_t *pt, int px, int py, int rr_s
     for (;;) {
         float t, hu, hv;
         pt->n_closest++;
+        log_ray(0, &ray);
         int64_t ti = scene_intersect(s, &ray, &t, &hu, &hv);
         if (ti < 0) break; /* on_miss is empty */
         const tri_t *tr = &s->tris[ti];
@@ -604,6 +616,7 @@ static void run_path(const oracle_scene *s, path_t *pt, int px, int py, int rr_s
                 v3 color = div3s(mul3(pt->beta, ff), light_pdf);
                 if (!is_black(color)) {
                     pt->n_shadow++;
+                    log_ray(1, &sh);
                     if (!scene_occlude(s, &sh)) pt->L = add3(pt->L, color);
                 }
             }
@@ -889,6 +902,22 @@ int akor_render(const oracle_scene *s, const akb_render_params *p, int x0, int y
                 int n_threads, uint64_t *counts) {
     const int32_t rect[4] = {x0, y0, x1, y1};
     return akor_render_rects(s, p, rect, 1, out_rgbw, n_threads, counts, NULL);
+}
+
+/* Diagnosis aid: every ray the Path integrator traces for pixel (x, y) over its p->spp samples, in order
+ * (9 floats each, see log_ray). Returns the number of rays (at most cap are stored). */
+int akor_pixel_rays(const oracle_scene *s, const akb_render_params *p, int x, int y, float *out, int cap) {
+    sampler_t smp; memset(&smp, 0, sizeof smp); smp.kind = p->sampler;
+    sampler_set_index(&smp, (uint64_t)(x + y * s->cam.w));
+    g_raylog = out; g_raylog_n = 0; g_raylog_cap = cap;
+    for (int k = 0; k < p->spp; k++) {
+        path_t pt; memset(&pt, 0, sizeof pt);
+        pt.beta = mk3(1, 1, 1); pt.max_depth = p->max_depth; pt.smp = smp;
+        run_path(s, &pt, x, y, p->rr_start_depth);
+        smp = pt.smp;
+    }
+    g_raylog = NULL;
+    return g_raylog_n;
 }
 
 int akor_generate_rays(const oracle_scene *s, const int32_t *xy, const float *u2, size_t n, float *org_tmin,

@@ -16,6 +16,8 @@
 #include <akari/kernel/bvh-accelerator.h>
 #include <akari/kernel/pathtracer.h>
 #include <akari/core/device.h>
+#include <akari/core/film.h>
+#include <akari/core/parallel.h>
 
 #include <atomic>
 #include <ctime>
@@ -394,6 +396,57 @@ int akref_render(void *h, const akb_render_params *p, int x0, int y0, int x1, in
                  int n_threads) {
     const int32_t rect[4] = {x0, y0, x1, y1};
     return akref_render_rects(h, p, rect, 1, out_rgbw, n_threads, nullptr);
+}
+
+// Film::write_image (core/film.h:97-113) -> GammaCorrection::process + DefaultImageWriter::write
+// (core/image.cpp:38-71), the reference's own byte stage, run on a film given as (sum R, sum G, sum B, sum weight)
+// per pixel: the sums enter a Film<C> through Tile::add_sample + Film::merge_tile (core/film.h:66-95), exactly as a
+// render leaves them. `path` ends in .png or .jpg.
+int akref_write_image(const float *rgbw, int w, int h, const char *path) {
+    AKR_IMPORT_TYPES()
+    try {
+        set_device_cpu();
+        Film<C> film(int2(w, h));
+        auto tile = film.tile(Bounds2i{int2(0), int2(w, h)});
+        for (int y = 0; y < h; y++)
+            for (int x = 0; x < w; x++) {
+                const float *p = rgbw + 4 * ((size_t)y * w + x);
+                tile.add_sample(float2(x, y), Spectrum(p[0], p[1], p[2]), p[3]);
+            }
+        film.merge_tile(tile);
+        film.write_image(fs::path(path));
+        return 0;
+    } catch (std::exception &e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+
+// DefaultImageReader::read (core/image.cpp:78-125): stbi_loadf for .hdr, stbi_load (byte / 255.0f) otherwise.
+// Returns RGBA float texels, top row first, as RGBAImage holds them. out may be NULL to query the size only.
+int akref_read_image(const char *path, int *w, int *h, float *out_rgba, size_t out_floats) {
+    try {
+        set_device_cpu();
+        auto img = default_image_reader()->read(fs::path(path));
+        if (!img)
+            return 1;
+        *w = img->resolution().x, *h = img->resolution().y;
+        if (!out_rgba)
+            return 0;
+        const size_t n = (size_t)*w * *h;
+        if (out_floats < 4 * n)
+            return 2;
+        for (int y = 0; y < *h; y++)
+            for (int x = 0; x < *w; x++) {
+                const auto &t = (*img)(x, y);
+                float *o = out_rgba + 4 * ((size_t)y * *w + x);
+                o[0] = t.rgb[0], o[1] = t.rgb[1], o[2] = t.rgb[2], o[3] = t.alpha;
+            }
+        return 0;
+    } catch (std::exception &e) {
+        g_err = e.what();
+        return 1;
+    }
 }
 
 } // extern "C"

@@ -129,6 +129,14 @@ class Oracle(_Base):
         self.busy = (float(busy[0]), float(busy[1]))
         return film
 
+    def pixel_rays(self, params, x, y, cap=65536):
+        """Every ray the Path integrator traces for pixel (x, y), in order: (is_any_hit[n], org_tmin[n,4], dir_tmax[n,4])."""
+        buf = np.zeros((cap, 9), np.float32)
+        n = self.lib.akor_pixel_rays(self.h, C.byref(params), int(x), int(y), _ptr(buf), cap)
+        r = buf[:n]
+        return (r[:, 0] != 0, np.ascontiguousarray(np.concatenate([r[:, 1:4], r[:, 7:8]], 1)),
+                np.ascontiguousarray(np.concatenate([r[:, 4:7], r[:, 8:9]], 1)))
+
     def film_to_srgb8(self, film):
         h, w = film.shape[:2]
         out = np.zeros((h, w, 3), np.uint8)
