@@ -29,14 +29,53 @@ def _ptr(a):
 
 _initialised = None
 
+# Development aid of THIS Python layer (the library itself never reads the environment): AKB_<OPTION>=value variables
+# are forwarded once to akb_set_option, so A/B scripts can flip a switch without editing code. tests use set_option().
+_ENV_OPTIONS = ("pipelines", "pipeline_min_slots", "graphs", "check_every", "poll_lag", "finish_div", "finish_max",
+                "no_park", "refill_below", "fetch_chunk", "profile_stages", "timeline", "trace_chunk", "trav_ifif",
+                "bvh_build", "bvh_verbose", "bvh_trav_cost", "bvh_prim_cost", "bvh_max_leaf", "bvh_device_algo",
+                "ploc_radius", "combine", "nvtx")
+_env_forwarded = False
+
+
+def _forward_env(lib):
+    global _env_forwarded
+    if _env_forwarded:
+        return
+    _env_forwarded = True
+    import os
+    for name in _ENV_OPTIONS:
+        v = os.environ.get("AKB_" + name.upper())
+        if v is not None:
+            _check(lib, lib.akb_set_option(name.encode(), v.encode()))
+
+
+def set_option(name, value):
+    """akb_set_option: a tuning switch of the library (csrc/options.h)."""
+    lib = abi.load()
+    _check(lib, lib.akb_set_option(str(name).encode(), str(value).encode()))
+
 
 def init(device_index=0):
-    """akb_init: bind this process to one GPU (one process per GPU)."""
+    """akb_init_device: bind this process to one GPU (the one-process-per-GPU arrangement)."""
     global _initialised
     lib = abi.load()
-    if _initialised != device_index:
-        _check(lib, lib.akb_init(device_index))
-        _initialised = device_index
+    _forward_env(lib)
+    if _initialised != ("device", device_index):
+        _check(lib, lib.akb_init_device(device_index))
+        _initialised = ("device", device_index)
+    return lib
+
+
+def init_multi(n_devices=0):
+    """akb_init(n_devices): bind this process to the first n GPUs (0 = all); scenes are replicated on all of them and
+    akb_render_params.n_gpus splits a frame over them."""
+    global _initialised
+    lib = abi.load()
+    _forward_env(lib)
+    if _initialised != ("multi", n_devices):
+        _check(lib, lib.akb_init(n_devices))
+        _initialised = ("multi", n_devices)
     return lib
 
 
@@ -49,9 +88,11 @@ class Backend:
     """A committed scene on the device: the replacement for `scene.accel = BVHAccelerator; scene.commit()` +
     `gpu::Integrator::render` (core/nodes/scene.cpp:119-162)."""
 
-    def __init__(self, scene, device_index=0, bvh_build=0):
-        """bvh_build: abi.BVH_DEFAULT / BVH_HOST_SAH / BVH_DEVICE (include/akari_b200.h akb_bvh_build)."""
-        self.lib = init(device_index)
+    def __init__(self, scene, device_index=0, bvh_build=0, n_devices=None):
+        """bvh_build: abi.BVH_DEFAULT / BVH_HOST_SAH / BVH_DEVICE (include/akari_b200.h akb_bvh_build).
+        n_devices: None = one process per GPU on `device_index`; a number = this process drives that many GPUs
+        (0 = all), the scene is replicated on each and render(params with n_gpus) splits the frame."""
+        self.lib = init(device_index) if n_devices is None else init_multi(n_devices)
         self.scene = scene
         self.width, self.height = scene.camera.resolution
         desc, keep = scene.flatten()
@@ -74,7 +115,8 @@ class Backend:
             pass
 
     def info(self):
-        keys = ["n_triangles", "n_bvh_nodes", "bvh_bytes", "n_lights", "triangle_bytes", "bvh_depth", "build_us", "bvh_build"]
+        keys = ["n_triangles", "n_bvh_nodes", "bvh_bytes", "n_lights", "triangle_bytes", "bvh_depth", "build_us", "bvh_build",
+                "n_devices", "upload_us"]
         return {k: int(self.lib.akb_scene_info(self.h, i)) for i, k in enumerate(keys)}
 
     # ---- Scene::intersect / occlude over host ray batches

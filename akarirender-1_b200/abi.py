@@ -6,7 +6,7 @@ built: there is no CPU fallback on the product path.
 import ctypes as C
 import os
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 OK, INVALID_ARG, CUDA_ERROR, NCCL_ERROR, OOM, NO_DEVICE = range(6)
 MAT_DIFFUSE, MAT_GLOSSY, MAT_EMISSIVE, MAT_MIX, MAT_DIELECTRIC = range(5)
@@ -50,14 +50,16 @@ class RenderParams(C.Structure):
     _fields_ = [("integrator", C.c_int32), ("spp", C.c_int32), ("max_depth", C.c_int32), ("ray_clamp", C.c_float),
                 ("sampler", C.c_int32), ("rr_start_depth", C.c_int32), ("mode", C.c_int32),
                 ("sort_materials", C.c_int32), ("ao_occlude", C.c_float), ("rank", C.c_int32),
-                ("world_size", C.c_int32), ("tile_size", C.c_int32), ("split", C.c_int32)]
+                ("world_size", C.c_int32), ("tile_size", C.c_int32), ("split", C.c_int32), ("n_gpus", C.c_int32),
+                ("_reserved", C.c_int32 * 3)]
 
 
 class RenderStats(C.Structure):
     _fields_ = [("n_samples", C.c_uint64), ("n_closest_rays", C.c_uint64), ("n_shadow_rays", C.c_uint64),
                 ("n_kernel_launches", C.c_uint64), ("ms_total", C.c_float), ("ms_raygen", C.c_float),
                 ("ms_extend", C.c_float), ("ms_shade", C.c_float), ("ms_shadow", C.c_float), ("ms_film", C.c_float),
-                ("ms_sort", C.c_float)]
+                ("ms_sort", C.c_float), ("n_gpus_used", C.c_int32), ("ms_combine", C.c_float), ("ms_wall", C.c_float),
+                ("_reserved", C.c_float)]
 
 
 class Hit(C.Structure):
@@ -66,7 +68,7 @@ class Hit(C.Structure):
 
 LIB_NAME = "libakari_b200.so"
 # every symbol include/akari_b200.h declares (tests check the built library exports all of them)
-SYMBOLS = ["akb_init", "akb_shutdown", "akb_last_error", "akb_device_count", "akb_scene_create", "akb_scene_destroy",
+SYMBOLS = ["akb_init", "akb_init_device", "akb_n_devices", "akb_set_option", "akb_shutdown", "akb_last_error", "akb_device_count", "akb_scene_create", "akb_scene_destroy",
            "akb_scene_info", "akb_render", "akb_render_device", "akb_trace", "akb_trace_device", "akb_generate_rays",
            "akb_film_to_srgb8", "akb_scene_file_load", "akb_scene_file_desc", "akb_scene_file_params",
            "akb_scene_file_output", "akb_scene_file_destroy", "akb_write_png", "akb_write_pfm"]
@@ -93,6 +95,12 @@ def load():
     vp, fp, ip = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32)
     L.akb_init.argtypes = [C.c_int]
     L.akb_init.restype = C.c_int
+    L.akb_init_device.argtypes = [C.c_int]
+    L.akb_init_device.restype = C.c_int
+    L.akb_n_devices.argtypes = []
+    L.akb_n_devices.restype = C.c_int
+    L.akb_set_option.argtypes = [C.c_char_p, C.c_char_p]
+    L.akb_set_option.restype = C.c_int
     L.akb_shutdown.argtypes = []
     L.akb_shutdown.restype = C.c_int
     L.akb_last_error.argtypes = []

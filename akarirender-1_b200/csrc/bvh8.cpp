@@ -3,6 +3,7 @@
 // quantisation. See bvh8.h. Replaces kernel/bvh-accelerator.h:72-87,125-475 (TBVHAccelerator build) of the
 // reference; the algorithm is different on purpose (no spatial splits, one level, wide nodes).
 #include "bvh8.h"
+#include "options.h"
 
 #include <stdlib.h>
 
@@ -30,14 +31,10 @@ inline float half_area(const float *lo, const float *hi) {
 }
 
 constexpr int kBins = 16;
-// Cost-model constants, overridable for tuning runs (AKB_BVH_TRAV_COST / AKB_BVH_PRIM_COST); see profiles/ for the sweep.
-static float env_float(const char *name, float dflt) {
-    const char *e = getenv(name);
-    return e && *e ? (float)atof(e) : dflt;
-}
-static const float kTraversalCost = env_float("AKB_BVH_TRAV_COST", 0.5f);
-// a CWBVH leaf slot addresses at most 3 triangles (unary-coded count); AKB_BVH_MAX_LEAF=1..3 for tuning runs
-static const int kMaxLeaf = std::min(3, std::max(1, (int)env_float("AKB_BVH_MAX_LEAF", 3.0f)));
+// Cost-model constants: akb_set_option("bvh_trav_cost" / "bvh_prim_cost" / "bvh_max_leaf") for tuning runs; see
+// profiles/ for the sweep. A CWBVH leaf slot addresses at most 3 triangles (unary-coded count).
+#define kTraversalCost (options().bvh_trav_cost)
+#define kMaxLeaf (options().bvh_max_leaf)
 
 struct Builder {
     const float *lo, *hi; // padded triangle boxes
@@ -273,7 +270,7 @@ struct Collapser {
     //   C_distribute(n,j) = min_{0<k<j} C(left,k) + C(right,j-k)
     // cost[n][i-1] = C(n,i); split[n][i-1] = k of the best distribution for i roots (0: use C(n,i-1));
     // kind[n]: the single-root choice (leaf or wide node); split8[n]: k of C_distribute(n,8).
-    const float kNodeCost = 1.0f, kPrimCost = env_float("AKB_BVH_PRIM_COST", 0.3f);
+    const float kNodeCost = 1.0f, kPrimCost = options().bvh_prim_cost;
     std::vector<float> cost;
     std::vector<uint8_t> split, split8, kind;
 
@@ -429,7 +426,7 @@ struct Collapser {
 } // namespace
 
 void bvh8_collapse_params(float *node_cost, float *prim_cost, int *max_leaf) {
-    *node_cost = 1.0f, *prim_cost = env_float("AKB_BVH_PRIM_COST", 0.3f), *max_leaf = kMaxLeaf;
+    *node_cost = 1.0f, *prim_cost = options().bvh_prim_cost, *max_leaf = kMaxLeaf;
 }
 
 void build_bvh8(const float *lo, const float *hi, size_t n, float pad, int n_threads, Bvh8 *out) {

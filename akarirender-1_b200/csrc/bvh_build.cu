@@ -5,6 +5,7 @@
 // is the root), leaf k (k-th triangle in Morton order) = node n-1+k. Binary nodes are never stored as such after the build: only their boxes, ranges and the
 // collapse DP tables live in HBM until the wide nodes are emitted.
 #include "bvh_build.cuh"
+#include "options.h"
 
 #include <math.h>
 #include <stdint.h>
@@ -480,8 +481,14 @@ __global__ void level_emit_kernel(TreeArrays T, int32_t *__restrict__ item_bnode
         }                                                                                                              \
     } while (0)
 
-struct Buffers {
+struct Buffers { // device scratch + timing events of one build; release() frees both (also on every error path)
     std::vector<void *> ptrs;
+    std::vector<cudaEvent_t> events;
+    cudaError_t event(cudaEvent_t *e) {
+        cudaError_t r = cudaEventCreate(e);
+        if (r == cudaSuccess) events.push_back(*e);
+        return r;
+    }
     template <class P> cudaError_t get(P **p, size_t count) {
         void *v = nullptr;
         cudaError_t e = cudaMalloc(&v, std::max<size_t>(count, 1) * sizeof(P));
@@ -492,6 +499,8 @@ struct Buffers {
     void release() {
         for (void *p : ptrs) cudaFree(p);
         ptrs.clear();
+        for (cudaEvent_t e : events) cudaEventDestroy(e);
+        events.clear();
     }
 };
 
@@ -507,11 +516,8 @@ cudaError_t build_bvh8_device(const float *lo, const float *hi, size_t n_tris, f
     const int n = (int)n_tris;
     Buffers bufs;
     cudaEvent_t ev[7];
-    for (auto &e : ev) CB(cudaEventCreate(&e));
-    auto done = [&]() {
-        for (auto &e : ev) cudaEventDestroy(e);
-        bufs.release();
-    };
+    for (auto &e : ev) CB(bufs.event(&e));
+    auto done = [&]() { bufs.release(); };
     float *d_lo, *d_hi;
     uint32_t *d_cb, *vals_in, *vals, *visit, *dp, *n_int, *n_tri, *off_int, *off_tri, *tri_order;
     uint64_t *keys_in, *keys;
@@ -543,11 +549,10 @@ cudaError_t build_bvh8_device(const float *lo, const float *hi, size_t n_tris, f
     CB(bufs.get(&nodes, n_tris + 1));
     CB(bufs.get(&tri_order, n_tris));
     T.n = n, T.dp = dp, T.visit = visit, T.vals = vals;
-    // binary topology: PLOC by default (near-SAH quality), AKB_BVH_DEVICE_ALGO=lbvh for the plain radix tree
-    const char *algo = getenv("AKB_BVH_DEVICE_ALGO");
-    const bool use_ploc = !(algo && !strcmp(algo, "lbvh"));
+    // binary topology: PLOC by default (near-SAH quality), akb_set_option("bvh_device_algo", "lbvh") for the plain radix tree
+    const bool use_ploc = !options().bvh_device_lbvh;
     int ploc_radius = 3, ploc_rounds = 0; // measured 1..32 on C3 and a clustered soup: 3-4 is best (profiles/r01c_notes.md)
-    if (const char *e = getenv("AKB_PLOC_RADIUS")) ploc_radius = std::min(kPlocMaxRadius, std::max(1, atoi(e)));
+    ploc_radius = std::min(kPlocMaxRadius, std::max(1, options().ploc_radius));
     uint32_t *cluster_a = nullptr, *cluster_b = nullptr;
     int32_t *nn = nullptr;
     unsigned long long *ploc_offs = nullptr;

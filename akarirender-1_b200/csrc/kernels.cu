@@ -678,6 +678,18 @@ __global__ void wf_resolve_kernel(RenderConfig rc, Workspace ws, float4 *__restr
     if (slot < ws.n_slots && slot_to_pixel(rc.map, slot + ws.slot_base, x, y)) film[(size_t)y * rc.map.width + x] = ws.acc[slot];
 }
 
+// dst (this GPU) += the peers' films, read over NVLink; fixed rank order, so the sum is reproducible
+__global__ void __launch_bounds__(256) film_sum_peers_kernel(float4 *__restrict__ dst, PeerFilms peers, size_t n_px) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_px; i += (size_t)gridDim.x * blockDim.x) {
+        float4 a = dst[i];
+        for (int k = 0; k < peers.n; k++) {
+            const float4 b = __ldcs(peers.film[k] + i);
+            a.x += b.x, a.y += b.y, a.z += b.z, a.w += b.w;
+        }
+        dst[i] = a;
+    }
+}
+
 template <class K> int blocks_per_sm(K kernel, int block) {
     int n = 1;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, block, 0) != cudaSuccess || n < 1) n = 1;
@@ -801,6 +813,13 @@ cudaError_t launch_wf_finish(const SceneDev &S, const RenderConfig &rc, const Wo
         wf_finish_kernel<AKB_SAMPLER_LCG, true><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
     else
         wf_finish_kernel<AKB_SAMPLER_LCG, false><<<grid, kBlock, 0, st>>>(S, rc, ws, parity);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_film_sum_peers(float4 *dst, const PeerFilms &peers, size_t n_px, int n_sms, cudaStream_t st) {
+    if (n_px == 0 || peers.n == 0) return cudaSuccess;
+    const int grid = (int)std::min<size_t>((n_px + 255) / 256, (size_t)n_sms * 8);
+    film_sum_peers_kernel<<<grid, 256, 0, st>>>(dst, peers, n_px);
     return cudaGetLastError();
 }
 

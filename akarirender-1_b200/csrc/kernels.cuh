@@ -72,4 +72,12 @@ cudaError_t launch_wf_finish(const SceneDev &S, const RenderConfig &rc, const Wo
                              cudaStream_t st);
 cudaError_t launch_wf_resolve(const RenderConfig &rc, const Workspace &ws, float4 *film, cudaStream_t st);
 
+// Sample-split combine over peer memory (akb_set_option("combine", "p2p")): dst[i] = ((dst[i] + film[0][i]) + film[1][i]) ...
+// in rank order, the peers' films read over NVLink by the GPU that owns dst.
+struct PeerFilms {
+    const float4 *film[15];
+    int n;
+};
+cudaError_t launch_film_sum_peers(float4 *dst, const PeerFilms &peers, size_t n_px, int n_sms, cudaStream_t st);
+
 } // namespace akb

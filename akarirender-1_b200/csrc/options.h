@@ -1,0 +1,41 @@
+// options.h — process-wide tuning switches of the library, set through akb_set_option(name, value) (include/akari_b200.h).
+// The library never reads the environment: a drop-in must not change behaviour on variables its host never heard of.
+// Defaults are the measured best on B200 (profiles/r01c_notes.md, profiles/r02_notes.md); none changes a result bit.
+#pragma once
+#include <string>
+
+namespace akb {
+
+struct Options {
+    // wavefront scheduling (api.cu)
+    int pipelines = 2;                   // half-frame pipelines of the wavefront (1 or 2)
+    int pipeline_min_slots = 128 * 1024; // below this many paths one pipeline keeps the launches large
+    int graphs = 1;                      // 0: launch every bounce's kernels one by one
+    int check_every = 4;                 // bounces per graph launch / queue-length poll (even)
+    int poll_lag = 1;                    // 0: wait for every queue-length poll
+    int finish_div = 4;                  // a pipeline whose queue is below slots / this is finished by wf_finish_kernel (0: never)
+    int finish_max = 1 << 16;            // ... and below this many paths
+    int no_park = 1;                     // 0: a path that ends with a shadow ray pending always waits one bounce for it
+    int refill_below = 0;                // persistent traversal warps refill below this many live lanes (0: 24 / 20 by step)
+    int fetch_chunk = 0;                 // >0: warp-private fetch chunks
+    int profile_stages = 0;              // per-stage events, one pipeline, no graphs, no finish kernel
+    int timeline = 0;                    // print every poll's device time and queue lengths
+    long long trace_chunk = 1ll << 21;   // rays per staging slot of akb_trace (host batches)
+    int trav_ifif = -1;                  // -1: if-if traversal step for trees of >= 64 nodes, fused below; 0 / 1 force
+    // BVH build (bvh8.cpp, bvh_build.cu)
+    int bvh_build = 0;        // akb_bvh_build used when the description says DEFAULT (0: by size)
+    int bvh_verbose = 0;      // build timings on stderr
+    float bvh_trav_cost = 0.5f, bvh_prim_cost = 0.3f;
+    int bvh_max_leaf = 3;     // a CWBVH leaf slot addresses at most 3 triangles
+    int bvh_device_lbvh = 0;  // 1: plain binary radix tree instead of PLOC
+    int ploc_radius = 3;
+    // multi-GPU frame (api.cu)
+    int combine = 0;          // 0: ncclReduce of the partial films; 1: peer-memory kernels over NVLink (no NCCL)
+    int nvtx = 1;             // NVTX ranges around render / trace / scene build
+};
+
+Options &options();
+// false (+ message) for an unknown name or an out-of-range value
+bool set_option(const char *name, const char *value, std::string *err);
+
+} // namespace akb

@@ -1,6 +1,7 @@
 // scene_host.cpp — see scene_host.h. Host arithmetic here must round exactly like the reference's host build:
 // compiled with -ffp-contract=off, fp32 expressions in the reference's order, glibc atanf.
 #include "scene_host.h"
+#include "options.h"
 
 #include <math.h>
 #include <string.h>
@@ -290,12 +291,85 @@ akb_status flatten_scene(const akb_scene_desc *d, int n_threads, HostScene *hs, 
         work();
         for (auto &t : th) t.join();
     }
-    if (getenv("AKB_BVH_VERBOSE")) {
+    if (options().bvh_verbose) {
         const auto t_b2 = std::chrono::steady_clock::now();
         fprintf(stderr, "[akb] flatten: records %.3f s, BVH %.3f s, leaf order %.3f s\n", std::chrono::duration<double>(t_b0 - t_f0).count(),
                 std::chrono::duration<double>(t_b1 - t_b0).count(), std::chrono::duration<double>(t_b2 - t_b1).count());
     }
     return AKB_OK;
+}
+
+Options &options() {
+    static Options o;
+    return o;
+}
+
+bool set_option(const char *name, const char *value, std::string *err) {
+    if (!name || !value) {
+        *err = "akb_set_option: null name or value";
+        return false;
+    }
+    Options &o = options();
+    const std::string n = name, v = value;
+    char *end = nullptr;
+    const double d = strtod(value, &end);
+    const bool numeric = end != value && *end == 0;
+    const long long i = (long long)d;
+    auto need = [&](bool ok) {
+        if (!ok) *err = "akb_set_option: bad value '" + v + "' for " + n;
+        return ok;
+    };
+#define AKB_INT_OPT(field, lo, hi)                                                                                     \
+    if (n == #field) {                                                                                                 \
+        if (!need(numeric && i >= (lo) && i <= (hi))) return false;                                                    \
+        o.field = (decltype(o.field))i;                                                                                \
+        return true;                                                                                                   \
+    }
+    AKB_INT_OPT(pipelines, 1, 2)
+    AKB_INT_OPT(pipeline_min_slots, 0, 1 << 30)
+    AKB_INT_OPT(graphs, 0, 1)
+    AKB_INT_OPT(poll_lag, 0, 1)
+    AKB_INT_OPT(finish_div, 0, 1 << 30)
+    AKB_INT_OPT(finish_max, 1, 1 << 30)
+    AKB_INT_OPT(no_park, 0, 1)
+    AKB_INT_OPT(refill_below, 0, 32)
+    AKB_INT_OPT(fetch_chunk, 0, 4096)
+    AKB_INT_OPT(profile_stages, 0, 1)
+    AKB_INT_OPT(timeline, 0, 1)
+    AKB_INT_OPT(trace_chunk, 1024, 1ll << 30)
+    AKB_INT_OPT(trav_ifif, -1, 1)
+    AKB_INT_OPT(bvh_verbose, 0, 1)
+    AKB_INT_OPT(bvh_max_leaf, 1, 3)
+    AKB_INT_OPT(ploc_radius, 1, 32)
+    AKB_INT_OPT(nvtx, 0, 1)
+#undef AKB_INT_OPT
+    if (n == "check_every") {
+        if (!need(numeric && i >= 2 && i <= 64)) return false;
+        o.check_every = (int)i & ~1;
+        return true;
+    }
+    if (n == "bvh_trav_cost" || n == "bvh_prim_cost") {
+        if (!need(numeric && d > 0)) return false;
+        (n == "bvh_trav_cost" ? o.bvh_trav_cost : o.bvh_prim_cost) = (float)d;
+        return true;
+    }
+    if (n == "bvh_build") {
+        if (!need(v == "default" || v == "host" || v == "device")) return false;
+        o.bvh_build = v == "host" ? AKB_BVH_HOST_SAH : (v == "device" ? AKB_BVH_DEVICE : AKB_BVH_DEFAULT);
+        return true;
+    }
+    if (n == "bvh_device_algo") {
+        if (!need(v == "ploc" || v == "lbvh")) return false;
+        o.bvh_device_lbvh = v == "lbvh";
+        return true;
+    }
+    if (n == "combine") {
+        if (!need(v == "nccl" || v == "p2p")) return false;
+        o.combine = v == "p2p";
+        return true;
+    }
+    *err = "akb_set_option: unknown option '" + n + "'";
+    return false;
 }
 
 SlotMap make_slot_map(int width, int height, int tile, int rank, int world) {

@@ -10,6 +10,7 @@
 
 #include <chrono>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/akari_b200.h"
@@ -28,7 +29,8 @@ static double now_s() {
 
 int main(int argc, char **argv) {
     const char *input = nullptr, *pfm = nullptr, *output = nullptr;
-    int device = 0, spp = -1, max_depth = -1, bvh = AKB_BVH_DEFAULT;
+    int device = -1, gpus = 1, spp = -1, max_depth = -1, bvh = AKB_BVH_DEFAULT, split = AKB_SPLIT_TILE;
+    std::vector<std::pair<std::string, std::string>> opts;
     for (int i = 1; i < argc; i++) {
         const std::string a = argv[i];
         auto next = [&]() -> const char * {
@@ -40,6 +42,17 @@ int main(int argc, char **argv) {
         };
         if (a == "--gpu" || a == "-v" || a == "--verbose") continue;
         else if (a == "-d" || a == "--device") device = atoi(next());
+        else if (a == "--gpus") gpus = atoi(next());
+        else if (a == "--split") split = std::string(next()) == "sample" ? AKB_SPLIT_SAMPLE : AKB_SPLIT_TILE;
+        else if (a == "--option") { // --option name=value -> akb_set_option
+            const std::string kv = next();
+            const size_t eq = kv.find('=');
+            if (eq == std::string::npos) {
+                fprintf(stderr, "akari-b200: --option wants name=value\n");
+                return 1;
+            }
+            opts.emplace_back(kv.substr(0, eq), kv.substr(eq + 1));
+        }
         else if (a == "--spp") spp = atoi(next());
         else if (a == "--max-depth") max_depth = atoi(next());
         else if (a == "--pfm") pfm = next();
@@ -53,16 +66,21 @@ int main(int argc, char **argv) {
         else input = argv[i];
     }
     if (!input) {
-        printf("usage: akari-b200 [--gpu] [-d device] [--spp N] [--max-depth N] [--bvh host|device] [-o out.png] [--pfm out.pfm] scene.akari\n");
+        printf("usage: akari-b200 [--gpu] [-d device | --gpus N [--split tile|sample]] [--option name=value] [--spp N] [--max-depth N] [--bvh host|device] [-o out.png] [--pfm out.pfm] scene.akari\n");
         return 0;
     }
-    CHECK(akb_init(device));
+    // --gpus N: the frame is split over the first N GPUs of this box (scene replicated, one film collective);
+    // -d D: the single device D
+    for (const auto &kv : opts) CHECK(akb_set_option(kv.first.c_str(), kv.second.c_str()));
+    if (device >= 0 && gpus <= 1) CHECK(akb_init_device(device));
+    else CHECK(akb_init(gpus < 1 ? 1 : gpus));
     akb_scene_file *file = nullptr;
     CHECK(akb_scene_file_load(input, &file));
     akb_render_params params;
     CHECK(akb_scene_file_params(file, &params));
     if (spp >= 0) params.spp = spp;
     if (max_depth >= 0) params.max_depth = max_depth;
+    params.n_gpus = gpus, params.split = split;
     akb_scene_desc desc_copy = *akb_scene_file_desc(file);
     desc_copy.bvh_build = (uint32_t)bvh;
     const akb_scene_desc *desc = &desc_copy;
@@ -79,9 +97,9 @@ int main(int argc, char **argv) {
     akb_render_stats st;
     t = now_s();
     CHECK(akb_render(scene, &params, film.data(), &st));
-    printf("render done took (%.3fs): %llu samples, %llu + %llu rays, %.1f Msamples/s on the device\n", now_s() - t,
+    printf("render done took (%.3fs): %llu samples, %llu + %llu rays, %.1f Msamples/s on %d GPU(s) (device time %.2f ms, film combine %.2f ms)\n", now_s() - t,
            (unsigned long long)st.n_samples, (unsigned long long)st.n_closest_rays, (unsigned long long)st.n_shadow_rays,
-           st.ms_total > 0 ? st.n_samples / (st.ms_total * 1e3) : 0.0);
+           st.ms_total > 0 ? st.n_samples / (st.ms_total * 1e3) : 0.0, st.n_gpus_used, st.ms_total, st.ms_combine);
     std::vector<uint8_t> rgb((size_t)W * H * 3);
     CHECK(akb_film_to_srgb8(film.data(), W, H, rgb.data()));
     const std::string out = output ? output : akb_scene_file_output(file);

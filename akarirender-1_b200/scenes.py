@@ -108,7 +108,7 @@ def multi_mesh_scene(n=20, resolution=(64, 36), spp=4, max_depth=5, coincident=F
     material remap). coincident=True puts the fourth mesh exactly on top of mesh 0 (the same triangles, so every hit on
     either is an exact-t tie between two meshes) plus one small triangle below the terrain.
     The scene stays at FOUR meshes on purpose: from five meshes on the reference's own TLAS loses meshes (measured with
-    oracle/_ref: 5x1, 3x2 and 5x2 placed copies are only ever hit on their last one or two meshes;
+    the reference build: 5x1, 3x2 and 5x2 placed copies are only ever hit on their last one or two meshes;
     BVHHandleConstructor, kernel/bvh-accelerator.h:643-648, stores the address of a constructor argument in every
     handle - a dangling pointer once the constructor returns), which is not behaviour to pin."""
     verts, tris, n_terrain = terrain_arrays(n)

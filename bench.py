@@ -286,17 +286,13 @@ def main():
     if rank == 0:
         peak, peak_src = measured_peaks()
         # ---- roofline of the dominant kernel (wf_trace): per-launch device time measured live with CUDA events on the
-        # launch stream (AKB_PROFILE_STAGES pass, outside the timed region), algorithmic bytes = 52 B per closest-hit
+        # launch stream (akb_set_option profile_stages pass, outside the timed region), algorithmic bytes = 52 B per closest-hit
         # ray + 36 B per any-hit ray.
         roof = None
         if a.mode == "wavefront" and world == 1:
-            os.environ["AKB_PROFILE_STAGES"] = "1"
-            pkg._initialised = None
-            pkg.init(local)
+            pkg.set_option("profile_stages", 1)
             stp = be.render_device(film.data_ptr(), p, stream)
-            os.environ["AKB_PROFILE_STAGES"] = "0"
-            pkg._initialised = None
-            pkg.init(local)
+            pkg.set_option("profile_stages", 0)
             n_launch = max(1, (stp.n_kernel_launches - 2) // 2)
             bytes_total = BYTES_CLOSEST * stp.n_closest_rays + BYTES_ANY * stp.n_shadow_rays
             achieved = bytes_total / (stp.ms_extend * 1e-3) / 1e9 if stp.ms_extend > 0 else None

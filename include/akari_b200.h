@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define AKB_ABI_VERSION 3
+#define AKB_ABI_VERSION 4
 
 typedef enum akb_status {
     AKB_OK = 0,
@@ -156,6 +156,12 @@ typedef struct akb_render_params {
     int32_t world_size;
     int32_t tile_size;
     int32_t split;          /* akb_split */
+    /* One process driving several GPUs (akb_init(n_devices >= 2)): akb_render splits the frame over the first n_gpus
+       initialised devices (`split`, `tile_size` as above; one host thread + stream per GPU inside the library), combines
+       the partial films with ONE collective on device 0 and returns the whole film. 0 or 1: one GPU. rank/world_size
+       must then be 0/0 or 0/1 (they describe the other arrangement: one process per GPU). */
+    int32_t n_gpus;
+    int32_t _reserved[3];
 } akb_render_params;
 
 /* Per-render statistics (the reference prints per-kernel cudaEvent stats, kernel/cuda/launch.cpp:92-118). */
@@ -166,6 +172,11 @@ typedef struct akb_render_stats {
     uint64_t n_kernel_launches;
     float ms_total;           /* device time of the whole render (CUDA events) */
     float ms_raygen, ms_extend, ms_shade, ms_shadow, ms_film, ms_sort; /* per-stage device time when profiled */
+    /* multi-GPU akb_render: counts above are sums over the GPUs, ms_total the slowest GPU's device time */
+    int32_t n_gpus_used;
+    float ms_combine;         /* host time of the film collective + its synchronisation */
+    float ms_wall;            /* host time of the whole call (render + combine + device-to-host copy) */
+    float _reserved;
 } akb_render_stats;
 
 /* Result of Scene::intersect (kernel/scene.h:40-49): prim_id/geom_id = -1 and t = +inf on a miss. */
@@ -179,10 +190,21 @@ typedef struct akb_scene akb_scene; /* opaque */
 
 /* ---- lifecycle --------------------------------------------------------------------------------------- */
 
-/* Replaces Device selection (cmd/akari.cpp:41-76 `--gpu`, core/device.cpp:142-183). Binds this process to
- * CUDA device `device_index` (one process per GPU). */
-akb_status akb_init(int device_index);
+/* Replaces Device selection (cmd/akari.cpp:41-76 `--gpu`, core/device.cpp:142-183): binds this process to the CUDA
+ * devices 0 .. n_devices-1 (0 = every visible device). Scenes created afterwards are replicated on all of them;
+ * akb_render_params.n_gpus chooses how many a frame uses. AKB_NO_DEVICE when fewer are usable. Calling it again
+ * re-binds (existing scenes must have been destroyed). */
+akb_status akb_init(int n_devices);
+/* The other arrangement, one process per GPU (torchrun / MPI: LOCAL_RANK): binds this process to the single device
+ * `device_index`; the caller passes rank/world_size in akb_render_params and combines the films itself. */
+akb_status akb_init_device(int device_index);
 akb_status akb_shutdown(void);
+/* Number of devices the last akb_init / akb_init_device bound (0 before). */
+int akb_n_devices(void);
+/* Tuning switches (csrc/options.h lists them; defaults are the measured best, none changes a result bit). The
+ * library never reads the environment. AKB_INVALID_ARG for an unknown name or a value out of range. Takes effect for
+ * scenes created / frames rendered afterwards. */
+akb_status akb_set_option(const char *name, const char *value);
 const char *akb_last_error(void);
 /* 0 when no CUDA device is usable. */
 int akb_device_count(void);
@@ -194,7 +216,8 @@ akb_status akb_scene_create(const akb_scene_desc *desc, akb_scene **out_scene);
 akb_status akb_scene_destroy(akb_scene *scene);
 
 /* Scene facts (for tests/benches): 0 n_triangles, 1 n_bvh_nodes, 2 bvh_bytes, 3 n_lights, 4 triangle_bytes,
- * 5 bvh_depth, 6 build_us (BVH build wall time), 7 the akb_bvh_build that produced the tree. */
+ * 5 bvh_depth, 6 build_us (BVH build wall time), 7 the akb_bvh_build that produced the tree, 8 the number of GPUs
+ * holding a replica, 9 upload_us (host-to-device copies of all replicas, wall time). */
 uint64_t akb_scene_info(const akb_scene *scene, int what);
 
 /* ---- the hot path ------------------------------------------------------------------------------------ */
@@ -202,7 +225,10 @@ uint64_t akb_scene_info(const akb_scene *scene, int what);
 /* Replaces gpu::Integrator<C>::render(const Scene<C>&, Film<C>*) (kernel/integrators/gpu/integrator.h:54-59,
  * called from SceneNode::render core/nodes/scene.cpp:141-162). Blocking. `out_rgbw` is a HOST buffer of
  * width*height*4 floats = (sum R, sum G, sum B, sum weight) per pixel, row-major: the contents of
- * Film::radiance / Film::weight after merge_tile (core/film.h:66-95). `stats` may be NULL. */
+ * Film::radiance / Film::weight after merge_tile (core/film.h:66-95). `stats` may be NULL.
+ * params->n_gpus >= 2: the frame is split over that many GPUs and combined on device 0 with one ncclReduce
+ * (AKB_NCCL_ERROR if NCCL cannot be loaded or fails; akb_set_option("combine", "p2p") uses the library's own
+ * peer-memory kernels over NVLink instead). With AKB_SPLIT_TILE the film is bit-identical to the one-GPU film. */
 akb_status akb_render(akb_scene *scene, const akb_render_params *params, float *out_rgbw, akb_render_stats *stats);
 
 /* Same, but the film stays in HBM: `d_out_rgbw` is a DEVICE pointer (width*height*4 floats) the caller owns

@@ -40,6 +40,7 @@ def test_no_cpu_fallback_without_a_device():
         pytest.skip("a CUDA device is present")
     assert lib.akb_init(0) == abi.NO_DEVICE
     assert b"no CPU fallback" in lib.akb_last_error()
+    assert lib.akb_init_device(0) == abi.NO_DEVICE and lib.akb_n_devices() == 0
     sc = scenes.cornell_box((8, 8), 1, 1)
     desc, keep = sc.flatten()
     h = C.c_void_p()
@@ -61,3 +62,20 @@ def test_product_package_never_touches_the_oracle():
                 txt = open(os.path.join(dp, f)).read()
                 assert "libakari_oracle" not in txt and "oracle/" not in txt.replace("oracle/akari_oracle.c", "") \
                     and "hostcheck" not in txt.replace("tests/hostcheck", ""), f
+
+
+def test_options_are_explicit_not_environment():
+    """Tuning goes through akb_set_option (no device needed to set one): unknown names and bad values are refused,
+    and the library's sources do not read the environment."""
+    lib = abi.load()
+    assert lib.akb_set_option(b"finish_div", b"8") == abi.OK
+    assert lib.akb_set_option(b"finish_div", b"4") == abi.OK
+    assert lib.akb_set_option(b"combine", b"p2p") == abi.OK and lib.akb_set_option(b"combine", b"nccl") == abi.OK
+    assert lib.akb_set_option(b"no_such_switch", b"1") == abi.INVALID_ARG
+    assert b"unknown option" in lib.akb_last_error()
+    assert lib.akb_set_option(b"pipelines", b"7") == abi.INVALID_ARG
+    assert lib.akb_set_option(b"bvh_build", b"maybe") == abi.INVALID_ARG
+    assert lib.akb_set_option(None, b"1") == abi.INVALID_ARG
+    for d in ("csrc", "host"):
+        for f in os.listdir(os.path.join(ROOT, "akarirender-1_b200", d)):
+            assert "getenv" not in open(os.path.join(ROOT, "akarirender-1_b200", d, f)).read(), f

@@ -121,13 +121,12 @@ def test_films_golden(G, S, mode):
 @pytest.mark.parametrize("name", ["cornell", "terrain"])
 def test_both_traversal_steps_bit_identical(G, S, name):
     """The persistent warps pick the if-if step for real trees and the fused step for tiny ones (api.cu); forcing
-    either (AKB_TRAV_IFIF, read at scene creation) must give the same hits, occlusion flags and film bits."""
+    either (akb_set_option trav_ifif) must give the same hits, occlusion flags and film bits."""
     sc = S[name]
     out = []
-    old = os.environ.get("AKB_TRAV_IFIF")
     try:
         for force in ("0", "1"):
-            os.environ["AKB_TRAV_IFIF"] = force
+            pkg.set_option("trav_ifif", force)  # read at scene creation
             be = backend(sc)
             h = be.trace(G[f"{name}_org2"], G[f"{name}_dir2"])
             occ = be.trace(G[f"{name}_org2"], G[f"{name}_dir2_any"], any_hit=True)
@@ -135,10 +134,7 @@ def test_both_traversal_steps_bit_identical(G, S, name):
             out.append((h.tobytes(), occ.tobytes(), film.tobytes()))
             be.close()
     finally:
-        if old is None:
-            os.environ.pop("AKB_TRAV_IFIF", None)
-        else:
-            os.environ["AKB_TRAV_IFIF"] = old
+        pkg.set_option("trav_ifif", "-1")
     assert out[0] == out[1]
     assert np.array_equal(np.frombuffer(out[0][1], np.int32), G[f"{name}_occ2"])
 
@@ -230,24 +226,22 @@ def test_finish_kernel_switch_point_and_parking_are_neutral():
     """Two scheduling choices of the wavefront that must not show in the results. (1) The tail of a frame is handed to
     wf_finish_kernel (one thread per remaining path) once a pipeline's queue is short: never, at the default point, or
     at the very first poll, when every path is still mid-flight with shadow rays pending and parked entries in the
-    queue. (2) A path that ends with a shadow ray pending either waits one bounce for it (AKB_NO_PARK=0) or lets the
+    queue. (2) A path that ends with a shadow ray pending either waits one bounce for it (option no_park = 0) or lets the
     traversal step add the finished sample to the film while the pixel already runs its next sample. Films and
-    sample/ray counts must be the same bits throughout (the switches are read by akb_init)."""
+    sample/ray counts must be the same bits throughout."""
     scs = (scenes.mixed_box((80, 56), 12, 5),
            scenes.terrain_scene(n=64, resolution=(96, 54), spp=12, max_depth=8, materials="c3", rr_start_depth=3),
            scenes.many_light_scene(n=48, resolution=(64, 36), spp=8, max_depth=16, n_quads=500))
-    keys = ("AKB_FINISH_DIV", "AKB_FINISH_MAX", "AKB_PIPELINE_MIN_SLOTS", "AKB_NO_PARK")
+    keys = ("finish_div", "finish_max", "pipeline_min_slots", "no_park")
     default = ("4", "65536", "131072", "1")
-    old = {k: os.environ.get(k) for k in keys}
     results = {}
+    backend(scs[0]).close()  # the library is initialised before options are pushed to the device
     try:
-        # akb_init only overrides what the environment names, so every setting is spelled out
         for cfg in (("0", "65536", "131072", "0"), ("0", "65536", "131072", "1"), default, ("8", "65536", "131072", "0"),
                     ("1", "100000000", "131072", "1"), ("1", "100000000", "1", "1"), ("1", "100000000", "1", "0"),
                     ("3", "100000000", "1", "1")):
-            os.environ.update(dict(zip(keys, cfg)))
-            pkg._initialised = None
-            pkg.init(0)
+            for k, v in zip(keys, cfg):
+                pkg.set_option(k, v)
             for i, sc in enumerate(scs):
                 be = backend(sc)
                 for sort in (0, 1):
@@ -260,13 +254,8 @@ def test_finish_kernel_switch_point_and_parking_are_neutral():
                 assert np.array_equal(results[(i, 0)][0], results[(i, 1)][0])
                 be.close()
     finally:
-        os.environ.update(dict(zip(keys, default)))
-        pkg._initialised = None
-        pkg.init(0)
-        for k, v in old.items():
-            os.environ.pop(k, None)
-            if v is not None:
-                os.environ[k] = v
+        for k, v in zip(keys, default):
+            pkg.set_option(k, v)
 
 
 def test_extensions_vs_oracle():
