@@ -4,7 +4,6 @@
 
 Select it at run time with AKB_LIB=/root/repo/akarirender-1_b200/libakari_b200_NAME.so (abi.lib_path)."""
 import os
-import subprocess
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -13,6 +12,4 @@ import __graft_entry__ as g  # noqa: E402
 
 name, extra = sys.argv[1], sys.argv[2:]
 out = os.path.join(g.PKG_DIR, "libakari_b200_%s.so" % name)
-srcs = [os.path.join(g.CSRC, s) for s in g.SOURCES]
-subprocess.run([os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")] + g.NVCC_FLAGS + extra + ["-o", out] + srcs, check=True, cwd=g.CSRC)
-print(out)
+print(g.build_library(force=True, out=out, extra_flags=extra))
