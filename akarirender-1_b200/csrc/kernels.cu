@@ -176,7 +176,6 @@ struct BatchSrc {
 __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS)
     trace_batch_kernel(SceneDev S, const float4 *__restrict__ org, const float4 *__restrict__ dir, uint32_t n, int any_hit,
                        akb_hit *__restrict__ hits, int32_t *__restrict__ occ, uint32_t *cursor) {
-    AKB_TRAV_PROLOGUE();
     BatchSrc src{org, dir, S.shading, hits, occ, any_hit != 0};
     persistent_trace(S.nodes, S.tris, src, n, cursor, S.trav_post_limit);
 }
@@ -213,7 +212,6 @@ __global__ void film_to_srgb8_kernel(const float4 *rgbw, size_t n, uint8_t *out)
 // samples, exactly the loop of cpu::PathTracer::render (kernel/integrators/cpu/integrator.cpp:121-135).
 template <int SAMP>
 __global__ void __launch_bounds__(kBlock) megakernel(SceneDev S, RenderConfig rc, float4 *__restrict__ film, Counters *ctr) {
-    AKB_TRAV_PROLOGUE();
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     int x = 0, y = 0;
     const bool valid = slot < rc.map.n_slots() && slot_to_pixel(rc.map, slot, x, y);
@@ -272,7 +270,6 @@ __global__ void __launch_bounds__(kBlock) megakernel(SceneDev S, RenderConfig rc
 template <int SAMP>
 __global__ void __launch_bounds__(kBlock) ao_kernel(SceneDev S, RenderConfig rc, float occlude, float4 *__restrict__ film,
                                                     Counters *ctr) {
-    AKB_TRAV_PROLOGUE();
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     int x = 0, y = 0;
     const bool valid = slot < rc.map.n_slots() && slot_to_pixel(rc.map, slot, x, y);
@@ -432,7 +429,6 @@ template <int SAMP> struct WfSrc {
 
 template <int SAMP>
 __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_trace_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
-    AKB_TRAV_PROLOGUE();
     Counters *ctr = ws.ctr;
     const uint32_t n_ext = ctr->n_ext[b], n_sh = ctr->n_sh[b];
     WfSrc<SAMP> src{S, rc, ws, b, n_ext};
@@ -584,7 +580,6 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
 // the ray counts do not depend on when the switch happens.
 template <int SAMP, bool TEX>
 __global__ void __launch_bounds__(kBlock) wf_finish_kernel(SceneDev S, RenderConfig rc, Workspace ws, int b) {
-    AKB_TRAV_PROLOGUE();
     Counters *ctr = ws.ctr;
     const uint32_t n = ctr->n_ext[b];
     unsigned long long n_closest = 0, n_shadow = 0, n_samples = 0;

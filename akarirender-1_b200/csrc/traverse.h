@@ -128,7 +128,7 @@ struct Trav {
     bool any, tri_popped;
     RayHit hit;
 #ifdef AKB_TRAV_STATS
-    uint32_t n_nodes, n_tris, n_child_hits;
+    uint32_t n_nodes, n_tris, n_child_hits, n_empty;
 #endif
 };
 
@@ -148,30 +148,32 @@ AKB_HD void trav_init(Trav &T, v3 o, v3 d, float tmin, float tmax, bool any_hit)
     T.hit.tri = -1, T.hit.t = INFINITY, T.hit.u = 0.f, T.hit.v = 0.f, T.hit.mat = -1;
 }
 
-// One node visit: pops a stack entry if the current node group is empty, intersects the eight quantised child boxes
-// and leaves the inner-child hits in T.ng and the leaf-triangle hits in (T.tri_base, T.tmask). A popped entry may also
-// be a postponed triangle group (y <= 0x00FFFFFF), which just becomes the current one. Returns false when there was
-// nothing left to do.
-AKB_HD bool trav_node(Trav &T, const float4 *__restrict__ nodes, uint2 *stack) {
-    uint2 ng = T.ng;
-    if (ng.y <= 0x00FFFFFFu) {
-        if (T.sp == 0) return false;
-        ng = stack[--T.sp];
-        if (ng.y <= 0x00FFFFFFu) { // postponed triangle group
-            T.tri_base = ng.x, T.tmask = ng.y;
-            T.ng.y = 0;
-            T.tri_popped = true; // must be tested now, not postponed again
-            return true;
-        }
-    }
-#ifdef AKB_TRAV_STATS
-    T.n_nodes++;
+// A traversal stack that would overflow silently drops the entry (release builds rely on the builders' depth bound,
+// kMaxBvh8Depth, which leaves room); -DAKB_DEBUG_TRAVERSAL traps instead.
+#if defined(AKB_DEBUG_TRAVERSAL) && defined(__CUDA_ARCH__)
+#define AKB_STACK_OVERFLOW() __trap()
+#elif defined(AKB_DEBUG_TRAVERSAL)
+#define AKB_STACK_OVERFLOW() __builtin_trap()
+#else
+#define AKB_STACK_OVERFLOW() ((void)0)
 #endif
+
+// THE node visit (the one copy all traversal steps share): takes the nearest pending child out of the node group `ng`
+// (pushing what is left of the group), loads that child node (five 128-bit loads), intersects its eight quantised
+// child boxes with the ray and returns the hit mask: bits 31..24 inner children in front-to-back order, bits 23..0
+// leaf triangles. On return `ng` is the visited node's own group (child base | inner hits | imask) and `tri_base` its
+// first leaf triangle.
+AKB_HD uint32_t visit_node(const Trav &T, uint2 &ng, uint2 *stack, int &sp, const float4 *__restrict__ nodes, uint32_t &tri_base) {
     const uint32_t oct_inv = T.oct_inv4 & 7u;
     const uint32_t imask = ng.y & 0xFFu;
     const int bit = akb_bfind(ng.y);
     ng.y &= ~(1u << bit);
-    if (ng.y > 0x00FFFFFFu && T.sp < kStackSize) stack[T.sp++] = ng;
+    if (ng.y > 0x00FFFFFFu) {
+        if (sp < kStackSize)
+            stack[sp++] = ng;
+        else
+            AKB_STACK_OVERFLOW();
+    }
     const uint32_t slot = (uint32_t)(bit - 24) ^ oct_inv;
     const uint32_t rel = (uint32_t)akb_popc(imask & ~(0xFFFFFFFFu << slot));
     const float4 *np = nodes + 5 * (size_t)(ng.x + rel);
@@ -217,21 +219,14 @@ AKB_HD bool trav_node(Trav &T, const float4 *__restrict__ nodes, uint2 *stack) {
         }
     }
     ng.y = (hitmask & 0xFF000000u) | (ew >> 24);
-    T.ng = ng;
-    T.tri_base = akb_f2u(n1.y);
-    T.tmask = hitmask & 0x00FFFFFFu;
-    T.tri_popped = false;
-#ifdef AKB_TRAV_STATS
-    T.n_tris += (uint32_t)akb_popc(T.tmask), T.n_child_hits += (uint32_t)akb_popc(hitmask >> 24);
-#endif
-    return true;
+    tri_base = akb_f2u(n1.y);
+    return hitmask;
 }
 
-// Tests ONE pending leaf triangle (T.tmask != 0). Returns true when an any-hit ray found its occluder.
-AKB_HD bool trav_tri(Trav &T, const float4 *__restrict__ tris) {
-    const int j = akb_bfind(T.tmask);
-    T.tmask &= ~(1u << j);
-    const float4 *tp = tris + 3 * (size_t)(T.tri_base + (uint32_t)j);
+// THE leaf-triangle test (shared by all traversal steps): leaf triangle `tri_base + j` against the ray, result folded
+// into the ray's best hit under the contract's tie rule. Returns true when an any-hit ray found its occluder.
+AKB_HD bool test_triangle(Trav &T, const float4 *__restrict__ tris, uint32_t tri_base, int j) {
+    const float4 *tp = tris + 3 * (size_t)(tri_base + (uint32_t)j);
     const float4 r0 = AKB_LD4(tp), r1 = AKB_LD4(tp + 1), r2 = AKB_LD4(tp + 2);
     float t, u, v;
     if (mt_test(T.o, T.d, T.tmin, T.any ? T.tbest : INFINITY, r0, r1, r2, t, u, v)) {
@@ -248,92 +243,63 @@ AKB_HD bool trav_tri(Trav &T, const float4 *__restrict__ tris) {
     return false;
 }
 
+// One node visit as a step of its own (tests/hostcheck's scheduling simulations): pops a stack entry if the current
+// node group is empty and leaves the inner-child hits in T.ng and the leaf-triangle hits in (T.tri_base, T.tmask). A
+// popped entry may also be a postponed triangle group (y <= 0x00FFFFFF), which just becomes the current one. Returns
+// false when there was nothing left to do.
+AKB_HD bool trav_node(Trav &T, const float4 *__restrict__ nodes, uint2 *stack) {
+    uint2 ng = T.ng;
+    if (ng.y <= 0x00FFFFFFu) {
+        if (T.sp == 0) return false;
+        ng = stack[--T.sp];
+        if (ng.y <= 0x00FFFFFFu) { // postponed triangle group
+            T.tri_base = ng.x, T.tmask = ng.y;
+            T.ng.y = 0;
+            T.tri_popped = true; // must be tested now, not postponed again
+            return true;
+        }
+    }
+    const uint32_t hitmask = visit_node(T, ng, stack, T.sp, nodes, T.tri_base);
+    T.ng = ng;
+    T.tmask = hitmask & 0x00FFFFFFu;
+    T.tri_popped = false;
+#ifdef AKB_TRAV_STATS
+    T.n_nodes++, T.n_empty += hitmask == 0;
+    T.n_tris += (uint32_t)akb_popc(T.tmask), T.n_child_hits += (uint32_t)akb_popc(hitmask >> 24);
+#endif
+    return true;
+}
+
+// Tests ONE pending leaf triangle (T.tmask != 0). Returns true when an any-hit ray found its occluder.
+AKB_HD bool trav_tri(Trav &T, const float4 *__restrict__ tris) {
+    const int j = akb_bfind(T.tmask);
+    T.tmask &= ~(1u << j);
+    return test_triangle(T, tris, T.tri_base, j);
+}
+
 AKB_HD bool trav_idle(const Trav &T) { return T.ng.y <= 0x00FFFFFFu && T.sp == 0 && T.tmask == 0; }
 
-// One node visit followed by all of its triangle tests, fused (this is the hot-loop form: the current node group and the
-// leaf hit mask live only in registers for the duration of the step). Returns true when the ray is finished (closest:
-// tree exhausted; any-hit: first accepted triangle, hit.tri = 0). Postponed triangle groups are never on the stack here.
+// One node visit followed by all of its triangle tests, fused (the form for tiny trees and for one ray per thread: the
+// current node group and the leaf hit mask live only in registers for the duration of the step). Returns true when
+// the ray is finished (closest: tree exhausted; any-hit: first accepted triangle, hit.tri = 0). Postponed triangle
+// groups are never on the stack here.
 AKB_HD bool trav_step(Trav &T, const float4 *__restrict__ nodes, const float4 *__restrict__ tris, uint2 *stack) {
     uint2 ng = T.ng;
     if (ng.y <= 0x00FFFFFFu) {
         if (T.sp == 0) return true;
         ng = stack[--T.sp];
     }
-#ifdef AKB_TRAV_STATS
-    T.n_nodes++;
-#endif
-    const uint32_t oct_inv = T.oct_inv4 & 7u;
-    const uint32_t imask = ng.y & 0xFFu;
-    const int bit = akb_bfind(ng.y);
-    ng.y &= ~(1u << bit);
-    if (ng.y > 0x00FFFFFFu && T.sp < kStackSize) stack[T.sp++] = ng;
-    const uint32_t slot = (uint32_t)(bit - 24) ^ oct_inv;
-    const uint32_t rel = (uint32_t)akb_popc(imask & ~(0xFFFFFFFFu << slot));
-    const float4 *np = nodes + 5 * (size_t)(ng.x + rel);
-    const float4 n0 = AKB_LD4(np), n1 = AKB_LD4(np + 1), n2 = AKB_LD4(np + 2), n3 = AKB_LD4(np + 3), n4 = AKB_LD4(np + 4);
-    const uint32_t ew = akb_f2u(n0.w);
-    const float idx = T.idx, idy = T.idy, idz = T.idz;
-    const float adjx = akb_u2f((ew & 0xFFu) << 23) * idx;
-    const float adjy = akb_u2f(((ew >> 8) & 0xFFu) << 23) * idy;
-    const float adjz = akb_u2f(((ew >> 16) & 0xFFu) << 23) * idz;
-    // plane distance = q*adj + (p - o)*idir with q carried as 32768 + q: fold the offset into the constant term
-    // (its rounding error, <= 2^-9 of a grid step, is covered by the builder's quantisation margin)
-    const float orgx = fmaf(-32768.0f, adjx, (n0.x - T.o.x) * idx);
-    const float orgy = fmaf(-32768.0f, adjy, (n0.y - T.o.y) * idy);
-    const float orgz = fmaf(-32768.0f, adjz, (n0.z - T.o.z) * idz);
-    ng.x = akb_f2u(n1.x);
-    const float tmin = T.tmin, tbest = T.tbest;
-    uint32_t hitmask = 0;
-    AKB_Q2F_SETUP();
-#pragma unroll
-    for (int half = 0; half < 2; half++) {
-        const uint32_t meta4 = akb_f2u(half ? n1.w : n1.z);
-        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-        const uint32_t inner_mask4 = akb_sext_s8x4(is_inner4 << 3);
-        const uint32_t bit_index4 = (meta4 ^ (T.oct_inv4 & inner_mask4)) & 0x1F1F1F1Fu;
-        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-        const uint32_t qlox = akb_f2u(half ? n2.y : n2.x), qloy = akb_f2u(half ? n2.w : n2.z);
-        const uint32_t qloz = akb_f2u(half ? n3.y : n3.x), qhix = akb_f2u(half ? n3.w : n3.z);
-        const uint32_t qhiy = akb_f2u(half ? n4.y : n4.x), qhiz = akb_f2u(half ? n4.w : n4.z);
-        const uint32_t nx = idx < 0 ? qhix : qlox, fx = idx < 0 ? qlox : qhix;
-        const uint32_t ny = idy < 0 ? qhiy : qloy, fy = idy < 0 ? qloy : qhiy;
-        const uint32_t nz = idz < 0 ? qhiz : qloz, fz = idz < 0 ? qloz : qhiz;
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const float tlx = fmaf(AKB_Q2F(nx, j), adjx, orgx);
-            const float tly = fmaf(AKB_Q2F(ny, j), adjy, orgy);
-            const float tlz = fmaf(AKB_Q2F(nz, j), adjz, orgz);
-            const float thx = fmaf(AKB_Q2F(fx, j), adjx, orgx);
-            const float thy = fmaf(AKB_Q2F(fy, j), adjy, orgy);
-            const float thz = fmaf(AKB_Q2F(fz, j), adjz, orgz);
-            const float cmin = fmaxf(fmaxf(tlx, tly), fmaxf(tlz, tmin));
-            const float cmax = fminf(fminf(thx, thy), fminf(thz, tbest));
-            if (cmin <= cmax) hitmask |= ((child_bits4 >> (8 * j)) & 0xFFu) << ((bit_index4 >> (8 * j)) & 0xFFu);
-        }
-    }
-    ng.y = (hitmask & 0xFF000000u) | (ew >> 24);
-    const uint32_t tri_base = akb_f2u(n1.y);
+    uint32_t tri_base;
+    const uint32_t hitmask = visit_node(T, ng, stack, T.sp, nodes, tri_base);
     uint32_t tmask = hitmask & 0x00FFFFFFu;
 #ifdef AKB_TRAV_STATS
+    T.n_nodes++, T.n_empty += hitmask == 0;
     T.n_tris += (uint32_t)akb_popc(tmask), T.n_child_hits += (uint32_t)akb_popc(hitmask >> 24);
 #endif
     while (tmask) {
         const int j = akb_bfind(tmask);
         tmask &= ~(1u << j);
-        const float4 *tp = tris + 3 * (size_t)(tri_base + (uint32_t)j);
-        const float4 r0 = AKB_LD4(tp), r1 = AKB_LD4(tp + 1), r2 = AKB_LD4(tp + 2);
-        float t, u, v;
-        if (mt_test(T.o, T.d, T.tmin, T.any ? T.tbest : INFINITY, r0, r1, r2, t, u, v)) {
-            if (T.any) {
-                T.hit.tri = 0;
-                return true;
-            }
-            const int id = (int)akb_f2u(r0.w);
-            if (t < T.tbest || (t == T.tbest && T.hit.tri >= 0 && id < T.hit.tri)) {
-                T.tbest = t;
-                T.hit.t = t, T.hit.u = u, T.hit.v = v, T.hit.tri = id, T.hit.mat = (int)akb_f2u(r1.w);
-            }
-        }
+        if (test_triangle(T, tris, tri_base, j)) return true;
     }
     T.ng = ng;
     return ng.y <= 0x00FFFFFFu && T.sp == 0;
@@ -369,59 +335,13 @@ AKB_HD bool trav_step_ii(Trav &T, const float4 *__restrict__ nodes, const float4
             }
         }
         if (visit) {
-            const uint32_t oct_inv = T.oct_inv4 & 7u;
-            const uint32_t imask = ng.y & 0xFFu;
-            const int bit = akb_bfind(ng.y);
-            ng.y &= ~(1u << bit);
-            if (ng.y > 0x00FFFFFFu && T.sp < kStackSize) stack[T.sp++] = ng;
-            const uint32_t slot = (uint32_t)(bit - 24) ^ oct_inv;
-            const uint32_t rel = (uint32_t)akb_popc(imask & ~(0xFFFFFFFFu << slot));
-            const float4 *np = nodes + 5 * (size_t)(ng.x + rel);
-            const float4 n0 = AKB_LD4(np), n1 = AKB_LD4(np + 1), n2 = AKB_LD4(np + 2), n3 = AKB_LD4(np + 3), n4 = AKB_LD4(np + 4);
-            const uint32_t ew = akb_f2u(n0.w);
-            const float idx = T.idx, idy = T.idy, idz = T.idz;
-            const float adjx = akb_u2f((ew & 0xFFu) << 23) * idx;
-            const float adjy = akb_u2f(((ew >> 8) & 0xFFu) << 23) * idy;
-            const float adjz = akb_u2f(((ew >> 16) & 0xFFu) << 23) * idz;
-            const float orgx = fmaf(-32768.0f, adjx, (n0.x - T.o.x) * idx);
-            const float orgy = fmaf(-32768.0f, adjy, (n0.y - T.o.y) * idy);
-            const float orgz = fmaf(-32768.0f, adjz, (n0.z - T.o.z) * idz);
-            ng.x = akb_f2u(n1.x);
-            const float tmin = T.tmin, tbest = T.tbest;
-            uint32_t hitmask = 0;
-            AKB_Q2F_SETUP();
-#pragma unroll
-            for (int half = 0; half < 2; half++) {
-                const uint32_t meta4 = akb_f2u(half ? n1.w : n1.z);
-                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                const uint32_t inner_mask4 = akb_sext_s8x4(is_inner4 << 3);
-                const uint32_t bit_index4 = (meta4 ^ (T.oct_inv4 & inner_mask4)) & 0x1F1F1F1Fu;
-                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-                const uint32_t qlox = akb_f2u(half ? n2.y : n2.x), qloy = akb_f2u(half ? n2.w : n2.z);
-                const uint32_t qloz = akb_f2u(half ? n3.y : n3.x), qhix = akb_f2u(half ? n3.w : n3.z);
-                const uint32_t qhiy = akb_f2u(half ? n4.y : n4.x), qhiz = akb_f2u(half ? n4.w : n4.z);
-                const uint32_t nx = idx < 0 ? qhix : qlox, fx = idx < 0 ? qlox : qhix;
-                const uint32_t ny = idy < 0 ? qhiy : qloy, fy = idy < 0 ? qloy : qhiy;
-                const uint32_t nz = idz < 0 ? qhiz : qloz, fz = idz < 0 ? qloz : qhiz;
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const float tlx = fmaf(AKB_Q2F(nx, j), adjx, orgx);
-                    const float tly = fmaf(AKB_Q2F(ny, j), adjy, orgy);
-                    const float tlz = fmaf(AKB_Q2F(nz, j), adjz, orgz);
-                    const float thx = fmaf(AKB_Q2F(fx, j), adjx, orgx);
-                    const float thy = fmaf(AKB_Q2F(fy, j), adjy, orgy);
-                    const float thz = fmaf(AKB_Q2F(fz, j), adjz, orgz);
-                    const float cmin = fmaxf(fmaxf(tlx, tly), fmaxf(tlz, tmin));
-                    const float cmax = fminf(fminf(thx, thy), fminf(thz, tbest));
-                    if (cmin <= cmax) hitmask |= ((child_bits4 >> (8 * j)) & 0xFFu) << ((bit_index4 >> (8 * j)) & 0xFFu);
-                }
-            }
-            ng.y = (hitmask & 0xFF000000u) | (ew >> 24);
+            uint32_t tri_base;
+            const uint32_t hitmask = visit_node(T, ng, stack, T.sp, nodes, tri_base);
             T.ng = ng;
             const uint32_t tm = hitmask & 0x00FFFFFFu;
             if (tm) {
                 if (T.tmask) stack[T.sp++] = uint2{T.tri_base, T.tmask}; // park the leftover group (room: post_limit)
-                T.tri_base = akb_f2u(n1.y), T.tmask = tm;
+                T.tri_base = tri_base, T.tmask = tm;
             }
         }
     }
@@ -430,21 +350,7 @@ AKB_HD bool trav_step_ii(Trav &T, const float4 *__restrict__ nodes, const float4
     if (live && T.tmask) {
         const int j = akb_bfind(T.tmask);
         T.tmask &= ~(1u << j);
-        const float4 *tp = tris + 3 * (size_t)(T.tri_base + (uint32_t)j);
-        const float4 r0 = AKB_LD4(tp), r1 = AKB_LD4(tp + 1), r2 = AKB_LD4(tp + 2);
-        float t, u, v;
-        if (mt_test(T.o, T.d, T.tmin, T.any ? T.tbest : INFINITY, r0, r1, r2, t, u, v)) {
-            if (T.any) {
-                T.hit.tri = 0;
-                done = true;
-            } else {
-                const int id = (int)akb_f2u(r0.w);
-                if (t < T.tbest || (t == T.tbest && T.hit.tri >= 0 && id < T.hit.tri)) {
-                    T.tbest = t;
-                    T.hit.t = t, T.hit.u = u, T.hit.v = v, T.hit.tri = id, T.hit.mat = (int)akb_f2u(r1.w);
-                }
-            }
-        }
+        done = test_triangle(T, tris, T.tri_base, j);
     }
     AKB_WARP_SYNC();
     return live && (done || (T.tmask == 0 && T.ng.y <= 0x00FFFFFFu && T.sp == 0));

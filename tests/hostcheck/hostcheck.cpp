@@ -357,21 +357,22 @@ extern "C" long hc_trig_mismatches(long n) {
     return bad;
 }
 
-// traversal statistics over a ray batch: out[0] node visits, out[1] triangle tests, out[2] inner-child hits
+// traversal statistics over a ray batch: out[0] node visits, out[1] triangle tests, out[2] inner-child hits,
+// out[3] node visits in which no child was hit
 extern "C" int hc_trace_stats(void *hv, const float *org, const float *dir, size_t n, int any_hit, double *out) {
     const SceneDev &S = ((HC *)hv)->dev;
-    double a = 0, b = 0, c = 0;
+    double a = 0, b = 0, c = 0, e = 0;
     for (size_t i = 0; i < n; i++) {
         Trav T;
         uint2 stack[kStackSize];
         trav_init(T, mk3(org[4 * i], org[4 * i + 1], org[4 * i + 2]), mk3(dir[4 * i], dir[4 * i + 1], dir[4 * i + 2]), org[4 * i + 3],
                   dir[4 * i + 3], any_hit != 0);
-        T.n_nodes = T.n_tris = T.n_child_hits = 0;
+        T.n_nodes = T.n_tris = T.n_child_hits = T.n_empty = 0;
         while (!trav_step(T, S.nodes, S.tris, stack)) {
         }
-        a += T.n_nodes, b += T.n_tris, c += T.n_child_hits;
+        a += T.n_nodes, b += T.n_tris, c += T.n_child_hits, e += T.n_empty;
     }
-    out[0] = a / n, out[1] = b / n, out[2] = c / n;
+    out[0] = a / n, out[1] = b / n, out[2] = c / n, out[3] = e / n;
     return 0;
 }
 
