@@ -85,6 +85,7 @@ __global__ void selftest_kernel(int *result, float a, float b, float c) {
 __constant__ int c_no_park = 1; // 0 (AKB_NO_PARK=0): a path that ends with a shadow ray pending always waits one step for it
 #define g_no_park c_no_park
 __constant__ int c_fetch_chunk = 0; // 0: reserve exactly the idle-lane count per refill; >0: warp-private chunks (AKB_FETCH_CHUNK)
+__constant__ int c_shade_partition = 0; // 1 (option shade_partition): a block regroups its 128 entries into hits | misses before shading (measured slower)
 __constant__ int c_refill_below = 0; // > 0: AKB_REFILL_BELOW override; else 24 with the if-if step, 20 with the fused one (measured best on B200)
 
 template <class Src>
@@ -379,7 +380,9 @@ template <int SAMP> struct WfSrc {
                 ws.hit[slot] = make_float4(T.hit.u, T.hit.v, __int_as_float(T.hit.tri), __int_as_float(T.hit.mat));
                 if (rc.sort_materials) {
                     key = 0;
-                    if (T.hit.tri >= 0 && T.hit.mat >= 0) {
+                    if (rc.sort_materials == 2) { // two queues only: hits | misses and parked entries
+                        key = T.hit.tri >= 0 ? 1 : 0;
+                    } else if (T.hit.tri >= 0 && T.hit.mat >= 0) {
                         // BSDF kind this vertex will evaluate: resolve Mix with the number the shade step will draw
                         // (second draw from the path's current sampler state = x of the next next2d()).
                         int type = S.mats[T.hit.mat].type;
@@ -460,22 +463,59 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
     }
     const uint32_t total = seg[kNumKeys];
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
     uint32_t n_done = 0, n_parked = 0;
-    for (uint32_t base = warp * 32u; base < total; base += n_warps * 32u) {
+    // Work is taken a block at a time: 128 consecutive queue entries, one warp per 32 of them, in queue order (which is
+    // near slot order, so the gathers of path state touch few lines). Option shade_partition = 1 first deals a block's
+    // entries out again so that warps are homogeneous - hits, which run path_vertex, then misses and parked entries,
+    // which only add to the film and regenerate; a STABLE two-way partition - and was measured SLOWER on B200 (C3 shade
+    // stage 8.84 vs 7.30 ms, C5 8.97 vs 6.47 ms; profiles/r02_notes.md): the three block barriers per round tie the
+    // four warps of a block to its slowest one, and the regrouped warps' gathers span twice the lines. Likewise two
+    // queues filled by the traversal step (hits | misses: sort_materials = 2) and the four BSDF-keyed queues
+    // (sort_materials = 1) lose to plain queue order: this kernel waits on memory, not on divergent issue slots.
+    __shared__ uint32_t s_slot[kBlock];
+    __shared__ float4 s_hit[kBlock];
+    __shared__ uint32_t s_warp_hits[kBlock / 32];
+    const bool partition = !rc.sort_materials && c_shade_partition;
+    for (uint32_t blk = blockIdx.x * kBlock; blk < total; blk += gridDim.x * kBlock) {
+        const uint32_t base = blk + (threadIdx.x & ~31u);
         int k = 0;
 #pragma unroll
         for (int q = 1; q < kNumKeys; q++)
             if (base >= seg[q]) k = q;
         const uint32_t j = base - seg[k] + lane;
-        const bool valid = j < cnt[k];
+        bool valid = j < cnt[k];
         bool push_ext = false, push_sh = false;
         uint32_t ext_entry = 0, slot = 0;
+        float4 hrec = make_float4(0.f, 0.f, 0.f, 0.f);
         if (valid) {
             slot = (rc.sort_materials ? ws.q_shade[b][k][j] : ws.q_ext[b][j]) & kSlotMask;
+            hrec = ws.hit[slot];
+        }
+        if (partition) {
+            const bool is_hit = valid && __float_as_int(hrec.z) >= 0;
+            const unsigned mh = __ballot_sync(0xffffffffu, is_hit), mv = __ballot_sync(0xffffffffu, valid);
+            if (lane == 0) s_warp_hits[threadIdx.x >> 5] = (uint32_t)__popc(mh) | ((uint32_t)__popc(mv) << 16);
+            __syncthreads();
+            uint32_t hits_before = 0, hits_total = 0, valid_before = 0, valid_total = 0;
+#pragma unroll
+            for (int w = 0; w < kBlock / 32; w++) {
+                const uint32_t c = s_warp_hits[w];
+                if (w < (int)(threadIdx.x >> 5)) hits_before += c & 0xFFFFu, valid_before += c >> 16;
+                hits_total += c & 0xFFFFu, valid_total += c >> 16;
+            }
+            if (valid) {
+                const uint32_t r_hit = hits_before + (uint32_t)__popc(mh & lanemask_lt());
+                const uint32_t r_all = valid_before + (uint32_t)__popc(mv & lanemask_lt());
+                const uint32_t dst = is_hit ? r_hit : hits_total + (r_all - r_hit);
+                s_slot[dst] = slot, s_hit[dst] = hrec;
+            }
+            __syncthreads();
+            valid = threadIdx.x < valid_total;
+            if (valid) slot = s_slot[threadIdx.x], hrec = s_hit[threadIdx.x];
+            __syncthreads(); // the arrays are rewritten by the next round
+        }
+        if (valid) {
             ext_entry = slot;
-            const float4 hrec = ws.hit[slot];
             const int tri = __float_as_int(hrec.z);
             PathState<SAMP> ps;
             ps.rng.s = ws.rng[slot];
@@ -700,6 +740,7 @@ template <class K> int blocks_per_sm(K kernel, int block) {
 
 cudaError_t set_refill_below(int v) { return cudaMemcpyToSymbol(c_refill_below, &v, sizeof(int)); }
 cudaError_t set_no_park(int v) { return cudaMemcpyToSymbol(c_no_park, &v, sizeof(int)); }
+cudaError_t set_shade_partition(int v) { return cudaMemcpyToSymbol(c_shade_partition, &v, sizeof(int)); }
 cudaError_t set_fetch_chunk(int v) { return cudaMemcpyToSymbol(c_fetch_chunk, &v, sizeof(int)); }
 
 cudaError_t launch_selftest(int *d_result, cudaStream_t st) {

@@ -53,6 +53,7 @@ cudaError_t launch_selftest(int *d_result, cudaStream_t st);
 cudaError_t set_refill_below(int v);
 cudaError_t set_fetch_chunk(int v);
 cudaError_t set_no_park(int v);
+cudaError_t set_shade_partition(int v);
 cudaError_t launch_trace_batch(const SceneDev &S, const float4 *org, const float4 *dir, size_t n, int any_hit,
                                akb_hit *hits, int32_t *occ, uint32_t *fetch_cursor, int n_sms, cudaStream_t st);
 cudaError_t launch_generate_rays(const SceneDev &S, const int32_t *xy, const float *u2, size_t n, float4 *org,

@@ -148,7 +148,8 @@ typedef struct akb_render_params {
     int32_t sampler;        /* akb_sampler; the reference hard-wires LCG (core/nodes/scene.cpp:126) */
     int32_t rr_start_depth; /* 0 = off (reference); >0: Russian roulette from this depth (extension) */
     int32_t mode;           /* akb_mode */
-    int32_t sort_materials; /* wavefront: order the shading wave by material id */
+    int32_t sort_materials; /* wavefront: 0 = shade in queue order (fastest measured); 1 = shading queues keyed by BSDF kind;
+                               2 = two queues, hits | misses. All give the same film bits. */
     float ao_occlude;       /* AO.occlude distance */
     /* image-space sharding: interleaved tile_size^2 tiles, owner = tile_id % world_size.
        Pixels this rank does not own are left at zero in the film. */

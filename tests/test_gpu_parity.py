@@ -211,15 +211,28 @@ def test_both_builders_on_triangle_soups_vs_brute_force(seed):
 
 
 def test_wavefront_equals_megakernel_and_sorting_is_neutral():
-    sc = scenes.mixed_box((80, 56), 6, 5)
-    be = backend(sc)
-    films = []
-    for mode, sort in ((abi.MODE_WAVEFRONT, 1), (abi.MODE_WAVEFRONT, 0), (abi.MODE_MEGAKERNEL, 0)):
-        p = sc.integrator.params()
-        p.mode, p.sort_materials = mode, sort
-        films.append(be.render(p)[0])
-    assert same_bits(films[0], films[1]) and same_bits(films[0], films[2])
-    be.close()
+    """Shading order is a scheduling choice: material-keyed queues, the block-level hits | misses regrouping of the
+    unsorted shade step (option shade_partition) and plain queue order all give the megakernel's film, bit for bit,
+    and the same sample / ray counts."""
+    for sc in (scenes.mixed_box((80, 56), 6, 5),
+               scenes.terrain_scene(n=64, resolution=(200, 120), spp=6, max_depth=8, materials="c3", rr_start_depth=3)):
+        be = backend(sc)
+        films, counts = [], []
+        try:
+            for mode, sort, part in ((abi.MODE_WAVEFRONT, 1, 0), (abi.MODE_WAVEFRONT, 2, 0), (abi.MODE_WAVEFRONT, 0, 1),
+                                     (abi.MODE_WAVEFRONT, 0, 0), (abi.MODE_MEGAKERNEL, 0, 0)):
+                pkg.set_option("shade_partition", part)
+                p = sc.integrator.params()
+                p.mode, p.sort_materials = mode, sort
+                film, st = be.render(p)
+                films.append(film)
+                if mode == abi.MODE_WAVEFRONT:
+                    counts.append((st.n_samples, st.n_closest_rays, st.n_shadow_rays))
+        finally:
+            pkg.set_option("shade_partition", 0)
+        assert all(same_bits(films[0], f) for f in films[1:])
+        assert all(c == counts[0] for c in counts[1:])
+        be.close()
 
 
 def test_finish_kernel_switch_point_and_parking_are_neutral():

@@ -81,7 +81,8 @@ def main():
         else:
             be = pkg.Backend(sc, 0)
         if "c3sort" in what:
-            frame(sc, "C3 %d spp" % spp, sort=1)
+            frame(sc, "C3 %d spp" % spp, sort=1).close()
+            frame(sc, "C3 %d spp" % spp, sort=2).close()
         if "rays" in what:
             rays(be, (1920, 1080))
         be.close()
