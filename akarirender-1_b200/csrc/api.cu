@@ -517,6 +517,7 @@ akb_status make_replica(const HostScene &hs, const Device &dev, Replica *r) {
         S.trav_post_limit = ifif ? std::max(0, kStackSize - hs.bvh.depth - 1) : -1;
     }
     S.n_textures = (int)(hs.tex_info.size() / 4);
+    S.n_nodes = (uint32_t)hs.bvh.nodes.size(), S.n_tris = (uint32_t)(hs.tris.size() / 3);
     S.cam = hs.cam;
     return AKB_OK;
 }
@@ -637,6 +638,7 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
                              bool film_is_shared, cudaStream_t stream, akb_render_stats *stats) {
     const Options &opt = options();
     CU(cudaSetDevice(r->dev.index));
+    CU(set_debug_bounds(r->S.n_nodes, r->S.n_tris));
     const int n_sms = r->dev.n_sms;
     akb_render_params q = *p;
     q.rank = rank, q.world_size = world;
@@ -1023,6 +1025,7 @@ akb_status akb_trace_device(akb_scene *sc, const float *d_org, const float *d_di
     NvtxRange range("akb_trace_device");
     Replica *r = sc->rep[0].get();
     CU(cudaSetDevice(r->dev.index));
+    CU(set_debug_bounds(r->S.n_nodes, r->S.n_tris));
     cudaStream_t stream = (cudaStream_t)cuda_stream;
     if (ms_kernel) CU(cudaEventRecord(r->ev0, stream));
     for (size_t off = 0; off < n; off += kMaxBatch) { // the kernel indexes rays with 32 bits
@@ -1046,6 +1049,7 @@ akb_status akb_trace(akb_scene *sc, const float *org, const float *dir, size_t n
     NvtxRange range("akb_trace");
     Replica *r = sc->rep[0].get();
     CU(cudaSetDevice(r->dev.index));
+    CU(set_debug_bounds(r->S.n_nodes, r->S.n_tris));
     const size_t out_elt = any_hit ? sizeof(int32_t) : sizeof(akb_hit);
     const size_t chunk = std::min<size_t>(n, (size_t)options().trace_chunk);
     cudaError_t e = cudaSuccess;

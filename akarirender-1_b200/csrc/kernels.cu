@@ -42,20 +42,21 @@ __device__ __forceinline__ unsigned lanemask_lt() {
 }
 
 // Warp-aggregated queue append; must be reached by all 32 lanes. One atomic per warp.
-__device__ __forceinline__ void queue_push(bool pred, uint32_t value, uint32_t *queue, uint32_t *counter) {
+__device__ __forceinline__ void queue_push(bool pred, uint32_t value, uint32_t *queue, uint32_t *counter, uint32_t cap) {
     const unsigned m = __ballot_sync(0xffffffffu, pred);
     if (m == 0) return;
     const int leader = __ffs(m) - 1;
     uint32_t base = 0;
     if ((int)(threadIdx.x & 31) == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
     base = __shfl_sync(0xffffffffu, base, leader);
+    AKB_CHECK(!pred || base + __popc(m & lanemask_lt()) < cap);
     if (pred) queue[base + __popc(m & lanemask_lt())] = value;
 }
 
 // Two appends at once (the shade step's extension and shadow queues): lanes 0 and 1 issue the two atomics in ONE
 // instruction, so the warp waits for one round trip to L2 instead of two.
 __device__ __forceinline__ void queue_push2(bool p0, uint32_t v0, uint32_t *q0, uint32_t *c0, bool p1, uint32_t v1, uint32_t *q1,
-                                            uint32_t *c1) {
+                                            uint32_t *c1, uint32_t cap) {
     const unsigned m0 = __ballot_sync(0xffffffffu, p0), m1 = __ballot_sync(0xffffffffu, p1);
     if ((m0 | m1) == 0) return;
     const unsigned lane = threadIdx.x & 31;
@@ -64,6 +65,8 @@ __device__ __forceinline__ void queue_push2(bool p0, uint32_t v0, uint32_t *q0, 
     uint32_t base = 0;
     if (lane < 2 && cnt) base = atomicAdd(ctr, cnt);
     const uint32_t b0 = __shfl_sync(0xffffffffu, base, 0), b1 = __shfl_sync(0xffffffffu, base, 1);
+    AKB_CHECK(!p0 || b0 + __popc(m0 & lanemask_lt()) < cap);
+    AKB_CHECK(!p1 || b1 + __popc(m1 & lanemask_lt()) < cap);
     if (p0) q0[b0 + __popc(m0 & lanemask_lt())] = v0;
     if (p1) q1[b1 + __popc(m1 & lanemask_lt())] = v1;
 }
@@ -343,7 +346,7 @@ template <int SAMP> __global__ void __launch_bounds__(256) wf_init_kernel(SceneD
             rng.set_sample_index((uint64_t)(x + y * rc.map.width) + rc.seed_offset);
             start_sample<SAMP>(S, ws, slot, x, y, rng, 0);
         }
-        queue_push(valid, (uint32_t)slot, ws.q_ext[0], &ws.ctr->n_ext[0]);
+        queue_push(valid, (uint32_t)slot, ws.q_ext[0], &ws.ctr->n_ext[0], (uint32_t)ws.n_slots);
     }
 }
 
@@ -359,6 +362,7 @@ template <int SAMP> struct WfSrc {
         if (i < n_ext) {
             const uint32_t e = ws.q_ext[b][i];
             slot = e & kSlotMask;
+            AKB_CHECK(slot < (uint32_t)ws.n_slots);
             if (e & kDeadRay) { // parked path: nothing to trace, the shade step just finishes it
                 T.hit.tri = -1, T.hit.mat = -1, T.any = false;
                 return false;
@@ -367,6 +371,7 @@ template <int SAMP> struct WfSrc {
             trav_init(T, xyz(o), xyz(d), o.w, d.w, false);
         } else {
             slot = ws.q_sh[b][i - n_ext];
+            AKB_CHECK(slot < (uint32_t)ws.n_slots);
             const float4 o = ws.sh_o[slot], d = ws.sh_d[slot];
             trav_init(T, xyz(o), xyz(d), o.w, d.w, true);
         }
@@ -424,6 +429,7 @@ template <int SAMP> struct WfSrc {
                 uint32_t qb = 0;
                 if ((int)lane == leader) qb = atomicAdd(&ws.ctr->n_shade[b][key], (uint32_t)__popc(grp));
                 qb = __shfl_sync(grp, qb, leader);
+                AKB_CHECK(qb + __popc(grp & lanemask_lt()) < (uint32_t)ws.n_slots);
                 ws.q_shade[b][key][qb + __popc(grp & lanemask_lt())] = slot;
             }
         }
@@ -596,7 +602,8 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
             }
         }
         if (push_sh) ext_entry |= kHasShadow; // a shadow ray always comes with an extension entry (continuing or parked)
-        queue_push2(push_ext, ext_entry, ws.q_ext[b ^ 1], &ctr->n_ext[b ^ 1], push_sh, slot, ws.q_sh[b ^ 1], &ctr->n_sh[b ^ 1]);
+        AKB_CHECK(!valid || slot < (uint32_t)ws.n_slots);
+        queue_push2(push_ext, ext_entry, ws.q_ext[b ^ 1], &ctr->n_ext[b ^ 1], push_sh, slot, ws.q_sh[b ^ 1], &ctr->n_sh[b ^ 1], (uint32_t)ws.n_slots);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
 #pragma unroll
@@ -738,6 +745,15 @@ template <class K> int blocks_per_sm(K kernel, int block) {
 
 } // namespace
 
+cudaError_t set_debug_bounds(uint32_t n_nodes, uint32_t n_tris) {
+#ifdef AKB_DEBUG_CHECKS
+    const uint32_t v[2] = {n_nodes, n_tris};
+    return cudaMemcpyToSymbol(c_dbg_bounds, v, sizeof v);
+#else
+    (void)n_nodes, (void)n_tris;
+    return cudaSuccess;
+#endif
+}
 cudaError_t set_refill_below(int v) { return cudaMemcpyToSymbol(c_refill_below, &v, sizeof(int)); }
 cudaError_t set_no_park(int v) { return cudaMemcpyToSymbol(c_no_park, &v, sizeof(int)); }
 cudaError_t set_shade_partition(int v) { return cudaMemcpyToSymbol(c_shade_partition, &v, sizeof(int)); }

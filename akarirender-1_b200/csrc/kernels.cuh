@@ -51,6 +51,7 @@ struct LaunchDims {
 
 cudaError_t launch_selftest(int *d_result, cudaStream_t st);
 cudaError_t set_refill_below(int v);
+cudaError_t set_debug_bounds(uint32_t n_nodes, uint32_t n_tris); // -DAKB_DEBUG_CHECKS builds only; a no-op otherwise
 cudaError_t set_fetch_chunk(int v);
 cudaError_t set_no_park(int v);
 cudaError_t set_shade_partition(int v);

@@ -90,6 +90,7 @@ struct SceneDev {
     int n_lights;
     int n_mats;
     int trav_post_limit; // traversal stack height below which a leftover triangle group may be parked (trav_step_ii)
+    uint32_t n_nodes, n_tris; // sizes of nodes / tris (bounds checks of the -DAKB_DEBUG_CHECKS build)
     // image textures (kernel/texture.h:39-57); n_textures == 0 for every BASELINE config, and then none of this is read
     int n_textures;
     const float4 *texels;   // all textures back to back, RGBA

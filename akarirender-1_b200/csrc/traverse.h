@@ -158,6 +158,20 @@ AKB_HD void trav_init(Trav &T, v3 o, v3 d, float tmin, float tmax, bool any_hit)
 #define AKB_STACK_OVERFLOW() ((void)0)
 #endif
 
+// -DAKB_DEBUG_CHECKS: bounds checks of our own on every node / triangle / queue / slot index (compute-sanitizer is not
+// available on the GPU pool): a violated check traps, which the host sees as a CUDA error from the next API call.
+#if defined(AKB_DEBUG_CHECKS) && defined(__CUDA_ARCH__)
+#define AKB_CHECK(cond)                                                                                                \
+    do {                                                                                                               \
+        if (!(cond)) __trap();                                                                                         \
+    } while (0)
+#else
+#define AKB_CHECK(cond) ((void)0)
+#endif
+#if defined(AKB_DEBUG_CHECKS) && defined(__CUDACC__)
+static __constant__ uint32_t c_dbg_bounds[2]; // node count, leaf-triangle count of the scene being rendered (kernels.cu sets them)
+#endif
+
 // THE node visit (the one copy all traversal steps share): takes the nearest pending child out of the node group `ng`
 // (pushing what is left of the group), loads that child node (five 128-bit loads), intersects its eight quantised
 // child boxes with the ray and returns the hit mask: bits 31..24 inner children in front-to-back order, bits 23..0
@@ -176,6 +190,7 @@ AKB_HD uint32_t visit_node(const Trav &T, uint2 &ng, uint2 *stack, int &sp, cons
     }
     const uint32_t slot = (uint32_t)(bit - 24) ^ oct_inv;
     const uint32_t rel = (uint32_t)akb_popc(imask & ~(0xFFFFFFFFu << slot));
+    AKB_CHECK(ng.x + rel < c_dbg_bounds[0]);
     const float4 *np = nodes + 5 * (size_t)(ng.x + rel);
     const float4 n0 = AKB_LD4(np), n1 = AKB_LD4(np + 1), n2 = AKB_LD4(np + 2), n3 = AKB_LD4(np + 3), n4 = AKB_LD4(np + 4);
     const uint32_t ew = akb_f2u(n0.w);
@@ -226,6 +241,7 @@ AKB_HD uint32_t visit_node(const Trav &T, uint2 &ng, uint2 *stack, int &sp, cons
 // THE leaf-triangle test (shared by all traversal steps): leaf triangle `tri_base + j` against the ray, result folded
 // into the ray's best hit under the contract's tie rule. Returns true when an any-hit ray found its occluder.
 AKB_HD bool test_triangle(Trav &T, const float4 *__restrict__ tris, uint32_t tri_base, int j) {
+    AKB_CHECK(tri_base + (uint32_t)j < c_dbg_bounds[1]);
     const float4 *tp = tris + 3 * (size_t)(tri_base + (uint32_t)j);
     const float4 r0 = AKB_LD4(tp), r1 = AKB_LD4(tp + 1), r2 = AKB_LD4(tp + 2);
     float t, u, v;
