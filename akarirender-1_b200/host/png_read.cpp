@@ -6,6 +6,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -63,8 +64,11 @@ const uint8_t kLenExtra[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3
 const uint16_t kDistBase[30] = {1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577};
 const uint8_t kDistExtra[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13};
 
-void inflate_block(BitReader &br, const Huffman &lit, const Huffman &dist, std::vector<uint8_t> &out) {
+// `limit`: the decoded size the caller expects (from IHDR); a stream that inflates beyond it is rejected before the
+// memory is spent (a small crafted file can expand 1000:1).
+void inflate_block(BitReader &br, const Huffman &lit, const Huffman &dist, std::vector<uint8_t> &out, size_t limit) {
     for (;;) {
+        if (out.size() > limit) throw std::runtime_error("image data longer than the header says");
         const int s = lit.decode(br);
         if (s < 256) {
             out.push_back((uint8_t)s);
@@ -82,10 +86,11 @@ void inflate_block(BitReader &br, const Huffman &lit, const Huffman &dist, std::
     }
 }
 
-std::vector<uint8_t> zlib_inflate(const std::vector<uint8_t> &z) {
+std::vector<uint8_t> zlib_inflate(const std::vector<uint8_t> &z, size_t limit) {
     if (z.size() < 6 || (z[0] & 0x0F) != 8 || ((z[0] << 8) | z[1]) % 31 != 0 || (z[1] & 0x20)) throw std::runtime_error("bad zlib header");
     BitReader br{z.data() + 2, z.data() + z.size()};
     std::vector<uint8_t> out;
+    out.reserve(std::min<size_t>(limit, (size_t)64 << 20));
     Huffman fixed_lit, fixed_dist;
     {
         uint8_t l[288];
@@ -104,10 +109,11 @@ std::vector<uint8_t> zlib_inflate(const std::vector<uint8_t> &z) {
             const uint32_t len = br.p[0] | (br.p[1] << 8), nlen = br.p[2] | (br.p[3] << 8);
             br.p += 4;
             if ((len ^ 0xFFFFu) != nlen || (size_t)(br.end - br.p) < len) throw std::runtime_error("bad stored block");
+            if (out.size() + len > limit) throw std::runtime_error("image data longer than the header says");
             out.insert(out.end(), br.p, br.p + len);
             br.p += len;
         } else if (type == 1) {
-            inflate_block(br, fixed_lit, fixed_dist, out);
+            inflate_block(br, fixed_lit, fixed_dist, out, limit);
         } else if (type == 2) {
             const int nlen = (int)br.bits(5) + 257, ndist = (int)br.bits(5) + 1, ncode = (int)br.bits(4) + 4;
             static const uint8_t order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
@@ -138,7 +144,7 @@ std::vector<uint8_t> zlib_inflate(const std::vector<uint8_t> &z) {
             Huffman lit, dist;
             lit.build(lengths, nlen);
             dist.build(lengths + nlen, ndist);
-            inflate_block(br, lit, dist, out);
+            inflate_block(br, lit, dist, out, limit);
         } else {
             throw std::runtime_error("bad deflate block type");
         }
@@ -177,10 +183,11 @@ void read_png_rgb8(const std::string &path, int *width, int *height, std::vector
         o += 12 + n;
     }
     if (w <= 0 || h <= 0 || ctype < 0) fail("no IHDR");
+    if (w > 65536 || h > 65536 || (size_t)w * h > ((size_t)1 << 28)) fail("image too large (limit 65536 x 65536, 2^28 pixels)");
     const int ch = ctype == 0 ? 1 : (ctype == 2 ? 3 : (ctype == 4 ? 2 : 4));
     std::vector<uint8_t> raw;
     try {
-        raw = zlib_inflate(idat);
+        raw = zlib_inflate(idat, ((size_t)w * ch + 1) * (size_t)h);
     } catch (const std::exception &e) {
         fail(e.what());
     }

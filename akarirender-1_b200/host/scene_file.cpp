@@ -111,19 +111,32 @@ struct Flattener {
     std::map<const Object *, int> index; // scene-wide material table, one entry per distinct node
     std::map<std::string, int> texture_of; // image textures by resolved path
 
-    // ImageTextureNode + DefaultImageReader (core/nodes/material.cpp:46-71, core/image.cpp:105-123): bytes / 255.0f,
-    // alpha 1. The reference opens the path relative to the directory of the file being parsed.
+    // ImageTextureNode + DefaultImageReader (core/nodes/material.cpp:46-71, core/image.cpp:78-125): `.hdr` files are
+    // float RGB as stored (stbi_loadf), everything else bytes / 255.0f (stbi_load), alpha 1. The reference opens the
+    // path relative to the directory of the file being parsed.
     int image_texture(const Object &o, const std::string &rel) {
         const std::string path = join_path(dir_of(o.file), rel);
         auto it = texture_of.find(path);
         if (it != texture_of.end()) return it->second;
         int w = 0, h = 0;
-        std::vector<uint8_t> rgb;
-        read_png_rgb8(path, &w, &h, &rgb);
-        auto tex = std::make_unique<std::vector<float>>((size_t)w * h * 4);
-        for (size_t i = 0; i < (size_t)w * h; i++) {
-            for (int k = 0; k < 3; k++) (*tex)[4 * i + k] = (float)rgb[3 * i + k] / 255.0f;
-            (*tex)[4 * i + 3] = 1.0f;
+        std::unique_ptr<std::vector<float>> tex;
+        const size_t dot = path.rfind('.');
+        if (dot != std::string::npos && path.substr(dot) == ".hdr") { // the reference decides by extension, exactly ".hdr"
+            std::vector<float> rgb;
+            read_hdr_rgb(path, &w, &h, &rgb);
+            tex = std::make_unique<std::vector<float>>((size_t)w * h * 4);
+            for (size_t i = 0; i < (size_t)w * h; i++) {
+                for (int k = 0; k < 3; k++) (*tex)[4 * i + k] = rgb[3 * i + k];
+                (*tex)[4 * i + 3] = 1.0f;
+            }
+        } else {
+            std::vector<uint8_t> rgb;
+            read_png_rgb8(path, &w, &h, &rgb);
+            tex = std::make_unique<std::vector<float>>((size_t)w * h * 4);
+            for (size_t i = 0; i < (size_t)w * h; i++) {
+                for (int k = 0; k < 3; k++) (*tex)[4 * i + k] = (float)rgb[3 * i + k] / 255.0f;
+                (*tex)[4 * i + 3] = 1.0f;
+            }
         }
         akb_texture d;
         d.width = w, d.height = h, d.rgba = tex->data();

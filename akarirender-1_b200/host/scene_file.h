@@ -40,6 +40,9 @@ void read_mesh_file(const std::string &path, MeshData *out);
 // 8-bit PNG -> tightly packed RGB bytes, the way `stbi_load(path, &x, &y, &channel, 3)` returns them
 // (core/image.cpp:105). png_read.cpp.
 void read_png_rgb8(const std::string &path, int *width, int *height, std::vector<uint8_t> *rgb);
+// Radiance .hdr -> RGB floats, the way `stbi_loadf(path, &x, &y, &channel, 3)` returns them (core/image.cpp:85-103).
+// hdr_read.cpp.
+void read_hdr_rgb(const std::string &path, int *width, int *height, std::vector<float> *rgb);
 
 // core/image.cpp:38-61 writes 8-bit PNG through stb; here: a self-contained PNG encoder (stored deflate blocks) and a
 // float PFM dump of radiance/weight (the reference has no float output).

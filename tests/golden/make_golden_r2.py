@@ -65,6 +65,46 @@ def srgb8_via_reference(film):
     return b.astype(np.uint8)
 
 
+def hdr_files(rng):
+    """Radiance .hdr files as bytes: flat pixels (width < 8), new-style RLE scanlines with runs and dumps, and the case
+    stb treats specially - a width in the RLE range whose data is not run-length encoded."""
+    def header(w, h, ident=b"#?RADIANCE"):
+        return ident + b"\n# made by make_golden_r2.py\nFORMAT=32-bit_rle_rgbe\nEXPOSURE=1.0\n\n-Y %d +X %d\n" % (h, w)
+
+    def rgbe(w, h):
+        px = rng.integers(0, 256, (h, w, 4)).astype(np.uint8)
+        px[..., 3] = rng.integers(118, 140, (h, w))  # exponents around 1.0
+        px[0, 0, 3] = 0                              # e = 0 -> black
+        px[..., :3][px[..., :3].max(-1) < 128] |= 128  # a valid RGBE pixel has one mantissa >= 128
+        return px
+
+    files = {}
+    p = rgbe(5, 4)
+    files["flat_5x4"] = header(5, 4) + p.tobytes()
+    p = rgbe(19, 6)
+    p[2, 3:15] = p[2, 3]  # a long run
+    body = b""
+    for row in p:
+        body += bytes([2, 2, 0, 19])
+        for k in range(4):
+            ch, i = row[:, k], 0
+            while i < 19:
+                j = i
+                while j + 1 < 19 and ch[j + 1] == ch[i] and j - i < 126:
+                    j += 1
+                if j - i >= 2:
+                    body += bytes([128 + (j - i + 1), ch[i]])
+                    i = j + 1
+                else:
+                    n = min(19 - i, int(rng.integers(1, 6)))
+                    body += bytes([n]) + ch[i:i + n].tobytes()
+                    i += n
+    files["rle_19x6"] = header(19, 6, b"#?RGBE") + body
+    p = rgbe(9, 3)
+    files["flatdata_9x3"] = header(9, 3) + p.tobytes()
+    return files
+
+
 def main():
     out = {}
     rng = np.random.default_rng(20261105)
@@ -113,6 +153,18 @@ def main():
     print("C1 full frame: reference differs from the brute-force oracle in", len(diff), "pixels:", diff.tolist())
     for b, r in zip(ans_b, ans_r):
         print("   brute", b, "reference", r)
+    # ---- .hdr image textures: the reference's reader (stbi_loadf, core/image.cpp:85-103) on small generated files
+    lib = C.CDLL(REF_SO)
+    for name, data in hdr_files(rng).items():
+        with tempfile.TemporaryDirectory() as td:
+            path = os.path.join(td, name + ".hdr")
+            open(path, "wb").write(data)
+            ww, hh = C.c_int(), C.c_int()
+            assert lib.akref_read_image(path.encode(), C.byref(ww), C.byref(hh), None, C.c_size_t(0)) == 0
+            tex = np.zeros((hh.value, ww.value, 4), np.float32)
+            assert lib.akref_read_image(path.encode(), C.byref(ww), C.byref(hh), tex.ctypes.data_as(C.c_void_p), C.c_size_t(tex.size)) == 0
+        out["hdr_" + name + "_file"] = np.frombuffer(data, np.uint8)
+        out["hdr_" + name + "_rgba"] = tex
     # ---- byte stage: the reference's own writer on golden films (incl. values <0.0031308, >1 and weight 0)
     G = np.load(os.path.join(HERE, "reference_vectors.npz"))
     for key in ("cornell32_film", "mixed32_film", "terrain_film"):
