@@ -159,6 +159,26 @@ def cpu_baseline_or_error(pkg, workload, spp, rows):
         return {"value": None, "unit": "Msamples/s", "cores": 0, "threads": os.cpu_count(), "kind": "port", "sample": "failed: %r" % (ex,)}
 
 
+def reference_gpu_run(pkg, workload, spp):
+    """The reference's OWN CUDA wavefront path tracer (oracle/_ref/libakari_ref_gpu.so: its gpu/cuda/integrator.cpp
+    patched in transit to build for sm_100a) on the same GPU: a comparison point, bounded in spp."""
+    from oracle_libs import ReferenceGPU, have_ref_gpu
+    if not have_ref_gpu():
+        return None
+    sc, name = make_scene(pkg, workload, spp, ref_subset=True)
+    W, H = sc.camera.resolution
+    p = sc.integrator.params()
+    p.ray_clamp = 10.0  # its GPU integrator always clamps
+    ref = ReferenceGPU(sc)
+    out = {"workload": name, "note": "reference gpu::PathTracer (tile 256, managed memory, --use_fast_math), render() + device sync, best of 2 after a warm-up"}
+    for label, wf in (("wavefront", True), ("megakernel", False)):
+        ref.render_gpu(p, 256, wf)
+        ms = min(ref.render_gpu(p, 256, wf)[1] for _ in range(2))
+        out[label] = {"value": W * H * sc.integrator.spp / ms / 1e3, "unit": "Msamples/s", "ms_per_step": ms}
+    ref.close()
+    return out
+
+
 def ncu_traffic():
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
@@ -342,6 +362,13 @@ def main():
             except Exception as ex:
                 subs["c2"] = {"error": repr(ex)}
             line["configs"] = subs
+            # the reference's own CUDA path tracer on this GPU (C1 as named; C3 at 16 spp: it needs 2 s per 16 spp)
+            try:
+                rg = {"c1": reference_gpu_run(pkg, "c1", 0), "c3_16spp": reference_gpu_run(pkg, "c3", 16)}
+                if rg["c1"]:
+                    line["reference_gpu"] = rg
+            except Exception as ex:
+                line["reference_gpu"] = {"error": repr(ex)}
         emit(line)
         return
     bench_multi(pkg, a, emit, rank, world, local, torch)

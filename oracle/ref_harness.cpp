@@ -12,11 +12,21 @@
 // the latter because Film keeps its float buffers private and can only write 8-bit PNG (core/film.h:76-113).
 // Built into oracle/_ref/libakari_ref.so (git-ignored). Used by tests/ (as the checker), tests/golden/make_golden.py
 // and bench.py's `--impl reference` / cpu_baseline legs only.
+//
+// Compiled a second time with -DAKREF_GPU by nvcc (oracle/Makefile target `ref_gpu`) together with
+// the reference's own CUDA wavefront (kernel/integrators/gpu/cuda/integrator.cpp, patched in transit by five sed
+// rules): then the scene lives in the reference's managed memory (set_device_gpu(); default_resource() = managed,
+// core/device.h:109) and akref_gpu_render() calls gpu::PathTracer<C>::render. Every allocation below therefore goes
+// through default_resource(), which is the host heap in the CPU build.
 #include <akari/kernel/scene.h>
 #include <akari/kernel/bvh-accelerator.h>
 #include <akari/kernel/pathtracer.h>
 #include <akari/core/device.h>
 #include <akari/core/film.h>
+#ifdef AKREF_GPU
+#include <akari/kernel/integrators/gpu/integrator.h>
+#include <chrono>
+#endif
 #include <akari/core/parallel.h>
 
 #include <atomic>
@@ -28,40 +38,49 @@
 
 #include "../include/akari_b200.h"
 
-using namespace akari;
+// Everything below sits inside namespace akari (the extern "C" entry points keep their plain C names): under nvcc the
+// reference's int2 / float2 / float3 would otherwise collide with CUDA's built-in vector types.
+namespace akari {
 using C = Config<float, Color<float, 3>>;
 
 namespace {
+    template <class T> using RVec = astd::pmr::vector<T>; // lives in default_resource(): host heap, or managed memory
+    template <class T> RVec<T> rvec(size_t n = 0) { return RVec<T>(n, TAllocator<T>(default_resource())); }
+
     struct RefScene {
         AKR_IMPORT_TYPES()
-        std::vector<std::vector<float>> P, N, UV;
-        std::vector<std::vector<int>> I, MI;
-        std::vector<std::vector<const Material<C> *>> mesh_mats;
-        std::vector<std::unique_ptr<Texture<C>>> textures;
+        std::vector<RVec<float>> P, N, UV;
+        std::vector<RVec<int>> I, MI;
+        std::vector<RVec<const Material<C> *>> mesh_mats;
+        std::vector<Texture<C> *> textures;
         std::vector<Material<C> *> materials; // scene table
-        std::vector<MeshInstance<C>> instances;
-        std::vector<AreaLight<C>> lights;
-        std::unique_ptr<Distribution1D<C>> light_distribution;
-        std::unique_ptr<BVHAccelerator<C>> accel;
+        RVec<MeshInstance<C>> instances = rvec<MeshInstance<C>>();
+        RVec<AreaLight<C>> lights = rvec<AreaLight<C>>();
+        Box<Distribution1D<C>> light_distribution;
+        Box<BVHAccelerator<C>> accel;
         Scene<C> scene;
         int width = 0, height = 0;
         ~RefScene() {
             for (auto *m : materials)
-                ::operator delete(m);
+                default_resource()->deallocate(m, sizeof(Material<C>), alignof(Material<C>));
+            for (auto *t : textures)
+                default_resource()->deallocate(t, sizeof(Texture<C>), alignof(Texture<C>));
         }
-        std::vector<std::vector<RGBA>> images; // texels of the description's image textures, as RGBAImage holds them
-        std::vector<int2> image_res;
-        Texture<C> *tex(float r, float g, float b) {
-            textures.emplace_back(new Texture<C>(ConstantTexture<C>(Spectrum(r, g, b))));
-            return textures.back().get();
+        std::vector<RVec<RGBA>> images; // texels of the description's image textures, as RGBAImage holds them
+        std::vector<akari::int2> image_res;
+        template <class... A> Texture<C> *new_tex(A &&...a) {
+            auto *t = (Texture<C> *)default_resource()->allocate(sizeof(Texture<C>), alignof(Texture<C>));
+            new (t) Texture<C>(std::forward<A>(a)...);
+            textures.push_back(t);
+            return t;
         }
+        Texture<C> *tex(float r, float g, float b) { return new_tex(ConstantTexture<C>(Spectrum(r, g, b))); }
         // constant unless the description names an image texture: then the reference's ImageTexture over those texels
         Texture<C> *tex(int image, float r, float g, float b) {
             if (image < 0)
                 return tex(r, g, b);
             RGBAImage::View view{images[image].data(), image_res[image]};
-            textures.emplace_back(new Texture<C>(ImageTexture<C>(view)));
-            return textures.back().get();
+            return new_tex(ImageTexture<C>(view));
         }
     };
 
@@ -99,7 +118,7 @@ namespace {
                 length(cross(triangle.vertices[1] - triangle.vertices[0], triangle.vertices[2] - triangle.vertices[0]));
             power.emplace_back(area * tc_area * I);
         }
-        rs.light_distribution.reset(new Distribution1D<C>(default_resource(), power.data(), power.size()));
+        rs.light_distribution = Box<Distribution1D<C>>::make(default_resource(), power.data(), power.size());
         scene.light_distribution = rs.light_distribution.get();
         scene.area_lights = BufferView<AreaLight<C>>(rs.lights.data(), rs.lights.size());
     }
@@ -116,20 +135,24 @@ void *akref_scene_create(const akb_scene_desc *d) {
             g_err = "bad desc";
             return nullptr;
         }
-        set_device_cpu(); // cmd/akari.cpp:41-76 does this before anything allocates (default_resource())
+#ifdef AKREF_GPU
+        set_device_gpu(); // cmd/akari.cpp:41-76 (`--gpu`) does this before anything allocates (default_resource())
+#else
+        set_device_cpu();
+#endif
         auto rs = std::make_unique<RefScene>();
         for (uint32_t i = 0; i < d->n_textures; i++) {
             const akb_texture &t = d->textures[i];
-            std::vector<RGBA> px((size_t)t.width * t.height);
+            RVec<RGBA> px = rvec<RGBA>((size_t)t.width * t.height);
             for (size_t k = 0; k < px.size(); k++)
-                px[k] = RGBA(float3(t.rgba[4 * k], t.rgba[4 * k + 1], t.rgba[4 * k + 2]), t.rgba[4 * k + 3]);
+                px[k] = RGBA(akari::float3(t.rgba[4 * k], t.rgba[4 * k + 1], t.rgba[4 * k + 2]), t.rgba[4 * k + 3]);
             rs->images.push_back(std::move(px));
-            rs->image_res.push_back(int2(t.width, t.height));
+            rs->image_res.push_back(akari::int2(t.width, t.height));
         }
         // materials: allocate raw storage first so Mix children can point at any entry
         rs->materials.resize(d->n_materials, nullptr);
         for (uint32_t i = 0; i < d->n_materials; i++)
-            rs->materials[i] = (Material<C> *)::operator new(sizeof(Material<C>));
+            rs->materials[i] = (Material<C> *)default_resource()->allocate(sizeof(Material<C>), alignof(Material<C>));
         for (uint32_t i = 0; i < d->n_materials; i++) {
             const akb_material &m = d->materials[i];
             switch (m.type) {
@@ -159,16 +182,23 @@ void *akref_scene_create(const akb_scene_desc *d) {
             }
         }
         size_t nm = d->n_meshes;
-        rs->P.resize(nm), rs->N.resize(nm), rs->UV.resize(nm), rs->I.resize(nm), rs->MI.resize(nm);
-        rs->mesh_mats.resize(nm);
+        for (size_t k = 0; k < nm; k++) {
+            rs->P.push_back(rvec<float>()), rs->N.push_back(rvec<float>()), rs->UV.push_back(rvec<float>());
+            rs->I.push_back(rvec<int>()), rs->MI.push_back(rvec<int>());
+            rs->mesh_mats.push_back(rvec<const Material<C> *>());
+        }
         rs->instances.resize(nm);
         for (size_t k = 0; k < nm; k++) {
             const akb_mesh &m = d->meshes[k];
-            rs->P[k].assign(m.vertices, m.vertices + 3 * m.n_vertices);
-            rs->N[k].assign(m.normals, m.normals + 9 * m.n_triangles);
-            rs->UV[k].assign(m.texcoords, m.texcoords + 6 * m.n_triangles);
-            rs->I[k].assign(m.indices, m.indices + 3 * m.n_triangles);
-            rs->MI[k].assign(m.material_indices, m.material_indices + m.n_triangles);
+            auto fill = [](auto &v, const auto *src, size_t n) { // astd::pmr::vector has no range assign
+                v.resize(n);
+                if (n) std::memcpy(v.data(), src, n * sizeof(*src));
+            };
+            fill(rs->P[k], m.vertices, 3 * m.n_vertices);
+            fill(rs->N[k], m.normals, 9 * m.n_triangles);
+            fill(rs->UV[k], m.texcoords, 6 * m.n_triangles);
+            fill(rs->I[k], m.indices, 3 * m.n_triangles);
+            fill(rs->MI[k], m.material_indices, m.n_triangles);
             for (int j = 0; j < m.n_mesh_materials; j++)
                 rs->mesh_mats[k].push_back(rs->materials[m.materials[j]]);
             MeshInstance<C> &inst = rs->instances[k];
@@ -185,10 +215,10 @@ void *akref_scene_create(const akb_scene_desc *d) {
         std::memcpy(cm, d->camera.c2w, sizeof(cm));
         Transform3f c2w{Matrix4f(cm)};
         rs->width = d->camera.width, rs->height = d->camera.height;
-        scene.camera = PerspectiveCamera<C>(int2(d->camera.width, d->camera.height), c2w, d->camera.fov);
+        scene.camera = PerspectiveCamera<C>(akari::int2(d->camera.width, d->camera.height), c2w, d->camera.fov);
         build_lights(*rs);
         scene.sampler = LCGSampler<C>(); // core/nodes/scene.cpp:126
-        rs->accel.reset(new BVHAccelerator<C>());
+        rs->accel = Box<BVHAccelerator<C>>::make();
         scene.accel = rs->accel.get(); // core/nodes/scene.cpp:129-130
         scene.commit();                // kernel/scene.cpp:64-81
         return rs.release();
@@ -251,8 +281,8 @@ int akref_generate_rays(void *h, const int32_t *xy, const float *u2, size_t n, f
     AKR_IMPORT_TYPES()
     auto *rs = (RefScene *)h;
     for (size_t i = 0; i < n; i++) {
-        auto s = rs->scene.camera.generate_ray(float2(0.5f, 0.5f), float2(u2[2 * i], u2[2 * i + 1]),
-                                               int2(xy[2 * i], xy[2 * i + 1]));
+        auto s = rs->scene.camera.generate_ray(akari::float2(0.5f, 0.5f), akari::float2(u2[2 * i], u2[2 * i + 1]),
+                                               akari::int2(xy[2 * i], xy[2 * i + 1]));
         org_tmin[4 * i] = s.ray.o.x, org_tmin[4 * i + 1] = s.ray.o.y, org_tmin[4 * i + 2] = s.ray.o.z;
         org_tmin[4 * i + 3] = s.ray.tmin;
         dir_tmax[4 * i] = s.ray.d.x, dir_tmax[4 * i + 1] = s.ray.d.y, dir_tmax[4 * i + 2] = s.ray.d.z;
@@ -355,7 +385,7 @@ int akref_render_rects(void *h, const akb_render_params *p, const int32_t *rects
                     for (int s = 0; s < spp; s++) {
                         sampler.start_next_sample();
                         if (ao) { // cpu/integrator.cpp:72-80
-                            CameraSample<C> sample = camera.generate_ray(sampler.next2d(), sampler.next2d(), int2(x, y));
+                            CameraSample<C> sample = camera.generate_ray(sampler.next2d(), sampler.next2d(), akari::int2(x, y));
                             auto L = ao_li(sample.ray, sampler);
                             weight += 1.0f;
                             sum += L;
@@ -365,7 +395,7 @@ int akref_render_rects(void *h, const akb_render_params *p, const int32_t *rects
                         pt.depth = 0;
                         pt.max_depth = max_depth;
                         pt.sampler = sampler;
-                        pt.run_megakernel(scene, camera, int2(x, y));
+                        pt.run_megakernel(scene, camera, akari::int2(x, y));
                         sampler = pt.sampler;
                         weight += 1.0f; // Tile::add_sample, core/film.h:66-70
                         sum += pt.L;
@@ -406,12 +436,12 @@ int akref_write_image(const float *rgbw, int w, int h, const char *path) {
     AKR_IMPORT_TYPES()
     try {
         set_device_cpu();
-        Film<C> film(int2(w, h));
-        auto tile = film.tile(Bounds2i{int2(0), int2(w, h)});
+        Film<C> film(akari::int2(w, h));
+        auto tile = film.tile(Bounds2i{akari::int2(0), akari::int2(w, h)});
         for (int y = 0; y < h; y++)
             for (int x = 0; x < w; x++) {
                 const float *p = rgbw + 4 * ((size_t)y * w + x);
-                tile.add_sample(float2(x, y), Spectrum(p[0], p[1], p[2]), p[3]);
+                tile.add_sample(akari::float2(x, y), Spectrum(p[0], p[1], p[2]), p[3]);
             }
         film.merge_tile(tile);
         film.write_image(fs::path(path));
@@ -449,4 +479,45 @@ int akref_read_image(const char *path, int *w, int *h, float *out_rgba, size_t o
     }
 }
 
+#ifdef AKREF_GPU
+// The reference's own CUDA wavefront / megakernel path tracer (gpu::PathTracer<C>::render,
+// kernel/integrators/gpu/cuda/integrator.cpp:206-424) on the committed scene; film sums as in akref_render.
+// ms_out (may be NULL): wall time of render() + device sync, as the reference's "render done took" measures it.
+int akref_gpu_render(void *h, const akb_render_params *p, int tile_size, int wavefront, float *out_rgbw, double *ms_out) {
+    AKR_IMPORT_TYPES()
+    try {
+        auto *rs = (RefScene *)h;
+        Scene<C> &scene = rs->scene;
+        scene.sampler = LCGSampler<C>();
+        Film<C> film(akari::int2(rs->width, rs->height));
+        gpu::PathTracer<C> pt(p->spp, p->max_depth, tile_size, p->ray_clamp, wavefront != 0);
+        const auto t0 = std::chrono::steady_clock::now();
+        pt.render(scene, &film);
+        active_device()->sync();
+        if (ms_out)
+            *ms_out = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        // Film keeps its float buffers private and only writes 8-bit images (core/film.h:72-113): read them through a
+        // struct of the same members in the same order.
+        struct FilmView {
+            TImage<Spectrum> radiance;
+            TImage<Float> weight;
+            Float splatScale;
+        };
+        static_assert(sizeof(FilmView) == sizeof(Film<C>), "Film layout changed");
+        const FilmView &fv = *reinterpret_cast<const FilmView *>(&film);
+        for (int y = 0; y < rs->height; y++)
+            for (int x = 0; x < rs->width; x++) {
+                float *o = out_rgbw + 4 * ((size_t)y * rs->width + x);
+                const auto L = fv.radiance(x, y);
+                o[0] = L[0], o[1] = L[1], o[2] = L[2], o[3] = fv.weight(x, y);
+            }
+        return 0;
+    } catch (std::exception &e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+#endif
+
 } // extern "C"
+} // namespace akari

@@ -172,6 +172,35 @@ class Reference(_Base):
         return film
 
 
+REF_GPU_SO = os.path.join(ROOT, "oracle", "_ref", "libakari_ref_gpu.so")
+
+
+def have_ref_gpu():
+    return os.path.exists(REF_GPU_SO)
+
+
+class ReferenceGPU(_Base):
+    """The reference's OWN CUDA wavefront path tracer (gpu::PathTracer, kernel/integrators/gpu/cuda/integrator.cpp),
+    patched in transit to compile for sm_100a (oracle/Makefile target ref_gpu). A comparison point
+    on the same box, not a parity oracle: it is built with --use_fast_math, draws one more random number per bounce and
+    clamps samples (gpu/cuda/integrator.cpp:286-287,397-398)."""
+    prefix = "akref"
+
+    def __init__(self, scene):
+        super().__init__(scene, C.CDLL(REF_GPU_SO))
+
+    def render_gpu(self, params, tile_size=256, wavefront=True):
+        """-> (film, milliseconds of render() + device sync)."""
+        film = np.zeros((self.height, self.width, 4), np.float32)
+        ms = C.c_double(0)
+        rc = self.lib.akref_gpu_render(self.h, C.byref(params), C.c_int(tile_size), C.c_int(int(wavefront)), _ptr(film),
+                                       C.byref(ms))
+        if rc != 0:
+            self.lib.akref_last_error.restype = C.c_char_p
+            raise RuntimeError(self.lib.akref_last_error().decode(errors="replace"))
+        return film, ms.value
+
+
 HOSTCHECK_DIR = os.path.join(ROOT, "tests", "hostcheck")
 HOSTCHECK_SO = os.path.join(HOSTCHECK_DIR, "libakari_hostcheck.so")
 CSRC = os.path.join(ROOT, "akarirender-1_b200", "csrc")
