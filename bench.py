@@ -302,6 +302,8 @@ def main():
     ap.add_argument("--mode", default="wavefront", choices=["wavefront", "megakernel"])
     ap.add_argument("--cpu-rows", type=int, default=96)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--reference-gpu", action="store_true",
+                    help="also time the reference's own CUDA path tracer (oracle/_ref/libakari_ref_gpu.so) on this GPU")
     ap.add_argument("--no-extras", action="store_true", help="skip the ray microbench and the other configs' sub-records")
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
@@ -362,7 +364,8 @@ def main():
             except Exception as ex:
                 subs["c2"] = {"error": repr(ex)}
             line["configs"] = subs
-            # the reference's own CUDA path tracer on this GPU (C1 as named; C3 at 16 spp: it needs 2 s per 16 spp)
+        if a.reference_gpu:
+            # opt-in: the reference's own CUDA path tracer on this GPU (C1 as named; C3 at 16 spp: it needs 2 s per 16 spp)
             try:
                 rg = {"c1": reference_gpu_run(pkg, "c1", 0), "c3_16spp": reference_gpu_run(pkg, "c3", 16)}
                 if rg["c1"]:
