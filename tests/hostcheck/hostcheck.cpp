@@ -376,6 +376,23 @@ extern "C" int hc_trace_stats(void *hv, const float *org, const float *dir, size
     return 0;
 }
 
+// per-ray work: node visits and triangle tests of every ray of a batch (the tail of this distribution is what a
+// traversal launch with few rays per thread waits for)
+extern "C" int hc_trace_counts(void *hv, const float *org, const float *dir, size_t n, int any_hit, uint32_t *nodes_out, uint32_t *tris_out) {
+    const SceneDev &S = ((HC *)hv)->dev;
+    for (size_t i = 0; i < n; i++) {
+        Trav T;
+        uint2 stack[kStackSize];
+        trav_init(T, mk3(org[4 * i], org[4 * i + 1], org[4 * i + 2]), mk3(dir[4 * i], dir[4 * i + 1], dir[4 * i + 2]), org[4 * i + 3],
+                  dir[4 * i + 3], any_hit != 0);
+        T.n_nodes = T.n_tris = T.n_child_hits = T.n_empty = 0;
+        while (!trav_step(T, S.nodes, S.tris, stack)) {
+        }
+        nodes_out[i] = T.n_nodes, tris_out[i] = T.n_tris;
+    }
+    return 0;
+}
+
 // Warp-level cost simulation of traversal scheduling policies (development aid): 32 lanes, rays fetched in order,
 // refill when fewer than `refill` lanes are busy. Costs in issued warp-instructions: node block cn, triangle round ct,
 // refill cf. policy 0: node step then all its triangles; 1: node block (lanes without pending triangles) + one triangle

@@ -39,7 +39,8 @@ def main():
         for _ in range(4):
             st = be.render_device(film.data_ptr(), p)
             best = min(best, st.ms_total)
-        out.append("rank %d: %.2f ms (%d launches)" % (rank, best, st.n_kernel_launches))
+        h = int(torch.sum(film.view(torch.int32).long() & 0xFFFFF).item())
+        out.append("rank %d: %.2f ms (%d launches, %d+%d rays, film-hash %d)" % (rank, best, st.n_kernel_launches, st.n_closest_rays, st.n_shadow_rays, h))
     ideal = None
     print("tile split 1/%d %s %s: %s" % (world, mode, opts, "; ".join(out)), flush=True)
     be.close()
