@@ -89,7 +89,86 @@ __constant__ int c_no_park = 1; // 0 (AKB_NO_PARK=0): a path that ends with a sh
 #define g_no_park c_no_park
 __constant__ int c_fetch_chunk = 0; // 0: reserve exactly the idle-lane count per refill; >0: warp-private chunks (AKB_FETCH_CHUNK)
 __constant__ int c_shade_partition = 0; // 1 (option shade_partition): a block regroups its 128 entries into hits | misses before shading (measured slower)
+__constant__ int c_tail_share = 1; // option tail_share: 0 never, 1 in launches of >= 4 rays per thread, 2 always: a drained warp's idle lanes help its busy ones
 __constant__ int c_refill_below = 0; // > 0: AKB_REFILL_BELOW override; else 24 with the if-if step, 20 with the fused one (measured best on B200)
+
+// The tail of a traversal launch. Once the queue is drained a warp cannot refill its idle lanes, and the launch lasts
+// as long as its slowest ray: one dependent chain of node visits (C3: mean 11, maximum 83 visits; 32 rays alone take
+// 70 us, 2 M rays 560 us). Here the lanes that have run out of rays take pending subtrees off the traversal stacks of
+// the lanes still busy and traverse them FOR THE SAME RAY: a helper lane copies the ray and the owner's best hit so far,
+// works through one stack entry (a node group or a parked triangle group) and hands its best hit back, which the owner
+// folds in under the contract's rule (nearest t, lowest triangle id among equal t) - the result is the minimum over
+// all accepted triangles whatever the order, so nothing changes but the latency. An any-hit ray ends for everybody
+// working on it as soon as one of them finds an occluder. Helpers hand out work themselves (root = the ray's owner).
+// Must be entered by all 32 lanes; returns when every ray of the warp has been completed through src.complete().
+template <class Src>
+__device__ __forceinline__ void tail_share(const float4 *__restrict__ nodes, const float4 *__restrict__ tris, Src &src, Trav &T, uint2 *stack,
+                                           bool active, uint32_t item, uint32_t tag, int post_limit) {
+    const unsigned full = 0xffffffffu;
+    const int lane = (int)(threadIdx.x & 31);
+    int root = -1;                         // >= 0: this lane is helping lane `root` with its ray
+    bool own_done = false, h_done = false; // owner finished its own share and waits for helpers / helper has a result to hand back
+    for (;;) {
+        if (trav_step_ii(T, nodes, tris, stack, active, post_limit)) {
+            active = false;
+            if (root >= 0)
+                h_done = true;
+            else
+                own_done = true;
+        }
+        for (unsigned hd = __ballot_sync(full, h_done); hd; hd &= hd - 1) { // helpers hand their best hit to the owner
+            const int l = __ffs(hd) - 1;
+            const int own = __shfl_sync(full, root, l);
+            if (own < 0) continue; // sent back to the idle pool a moment ago: another helper found the ray's occluder
+            const float ht = __shfl_sync(full, T.hit.t, l), hu = __shfl_sync(full, T.hit.u, l), hv = __shfl_sync(full, T.hit.v, l);
+            const int htri = __shfl_sync(full, T.hit.tri, l), hmat = __shfl_sync(full, T.hit.mat, l);
+            const bool occluder = __shfl_sync(full, (int)T.any, l) != 0 && htri >= 0;
+            if (lane == own) {
+                if (occluder) {
+                    T.hit.tri = 0, active = false, own_done = true;
+                } else if (!T.any && htri >= 0 && (ht < T.tbest || (ht == T.tbest && T.hit.tri >= 0 && htri < T.hit.tri))) {
+                    T.tbest = ht;
+                    T.hit.t = ht, T.hit.u = hu, T.hit.v = hv, T.hit.tri = htri, T.hit.mat = hmat;
+                }
+            }
+            if (lane == l || (occluder && root == own)) active = false, h_done = false, root = -1; // back to the idle pool
+        }
+        const unsigned grp = __match_any_sync(full, root >= 0 ? root : lane); // an owner and everybody helping it
+        bool have = false;
+        if (own_done && __popc(grp) == 1) own_done = false, have = true;
+        if (__any_sync(full, have)) src.complete(have, item, tag, T);
+        const unsigned idle = __ballot_sync(full, !active && !own_done), donors = __ballot_sync(full, active && T.sp > 0);
+        if (idle && donors) {
+            const int n_pair = min(__popc(idle), __popc(donors));
+            const bool give = active && T.sp > 0 && __popc(donors & lanemask_lt()) < n_pair;
+            const bool take = !active && !own_done && __popc(idle & lanemask_lt()) < n_pair;
+            uint2 e = make_uint2(0u, 0u);
+            if (give) e = stack[--T.sp]; // (handing out the bottom entry instead - the farthest subtree - measured the same)
+            const int from = take ? (int)__fns(donors, 0, __popc(idle & lanemask_lt()) + 1) : lane;
+            const float ox = __shfl_sync(full, T.o.x, from), oy = __shfl_sync(full, T.o.y, from), oz = __shfl_sync(full, T.o.z, from);
+            const float dx = __shfl_sync(full, T.d.x, from), dy = __shfl_sync(full, T.d.y, from), dz = __shfl_sync(full, T.d.z, from);
+            const float ix = __shfl_sync(full, T.idx, from), iy = __shfl_sync(full, T.idy, from), iz = __shfl_sync(full, T.idz, from);
+            const float tmn = __shfl_sync(full, T.tmin, from), tbs = __shfl_sync(full, T.tbest, from);
+            const uint32_t oct = __shfl_sync(full, T.oct_inv4, from);
+            const int any = __shfl_sync(full, (int)T.any, from), r_root = __shfl_sync(full, root >= 0 ? root : lane, from);
+            const float ht = __shfl_sync(full, T.hit.t, from), hu = __shfl_sync(full, T.hit.u, from), hv = __shfl_sync(full, T.hit.v, from);
+            const int htri = __shfl_sync(full, T.hit.tri, from), hmat = __shfl_sync(full, T.hit.mat, from);
+            const uint32_t ex = __shfl_sync(full, e.x, from), ey = __shfl_sync(full, e.y, from);
+            if (take) {
+                T.o = mk3(ox, oy, oz), T.d = mk3(dx, dy, dz), T.idx = ix, T.idy = iy, T.idz = iz, T.tmin = tmn, T.tbest = tbs;
+                T.oct_inv4 = oct, T.any = any != 0;
+                T.hit.t = ht, T.hit.u = hu, T.hit.v = hv, T.hit.tri = T.any ? -1 : htri, T.hit.mat = hmat;
+                T.sp = 0, T.tri_popped = false;
+                if (ey > 0x00FFFFFFu) // a node group: the remaining children of a visited node
+                    T.ng = make_uint2(ex, ey), T.tri_base = 0, T.tmask = 0;
+                else // a parked triangle group
+                    T.ng = make_uint2(0u, 0u), T.tri_base = ex, T.tmask = ey;
+                root = r_root, active = true;
+            }
+        }
+        if (!__any_sync(full, active || own_done)) break;
+    }
+}
 
 template <class Src>
 __device__ __forceinline__ void persistent_trace(const float4 *__restrict__ nodes, const float4 *__restrict__ tris, Src &src,
@@ -138,6 +217,16 @@ __device__ __forceinline__ void persistent_trace(const float4 *__restrict__ node
         // (Batching the leaf-triangle tests across lanes - one Moeller-Trumbore round per iteration, or only once N
         // lanes wait - was measured on B200 and did not pay: the node block then runs with fewer lanes (20 instead of
         // 26 of 32) and total issued instructions stay within 5 %; profiles/r01c_notes.md.)
+        // (only for launches with at least four rays per thread, or option tail_share = 2: a launch with one or two rays per
+        // thread is all tail, and there the helpers' extra node fetches cost more than the shorter chains win - measured
+        // on a 1/8 tile-split share of C3: 34.4 vs 29.9 ms; full frame: 27.8 vs 28.3 ms; 2 M incoherent rays: +5 % closest,
+        // +10 % any hit)
+        if (no_more && post_limit >= 0 && (c_tail_share == 2 || (c_tail_share == 1 && total >= 4u * gridDim.x * blockDim.x))) {
+            src.complete(have, item, tag, T); // entries the refill above found ready (parked paths)
+            have = false;
+            tail_share(nodes, tris, src, T, stack, active, item, tag, post_limit);
+            break; // every lane's ray is finished and consumed
+        }
         do {
             // post_limit >= 0: the "if-if" step (one node visit + one triangle test per lane and iteration, traverse.h);
             // < 0: the fused step, which is better for tiny trees where a ray is a handful of steps
@@ -756,6 +845,7 @@ cudaError_t set_debug_bounds(uint32_t n_nodes, uint32_t n_tris) {
 }
 cudaError_t set_refill_below(int v) { return cudaMemcpyToSymbol(c_refill_below, &v, sizeof(int)); }
 cudaError_t set_no_park(int v) { return cudaMemcpyToSymbol(c_no_park, &v, sizeof(int)); }
+cudaError_t set_tail_share(int v) { return cudaMemcpyToSymbol(c_tail_share, &v, sizeof(int)); }
 cudaError_t set_shade_partition(int v) { return cudaMemcpyToSymbol(c_shade_partition, &v, sizeof(int)); }
 cudaError_t set_fetch_chunk(int v) { return cudaMemcpyToSymbol(c_fetch_chunk, &v, sizeof(int)); }
 

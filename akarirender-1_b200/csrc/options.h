@@ -17,6 +17,8 @@ struct Options {
     int finish_max = 1 << 16;            // ... and below this many paths
     int no_park = 1;                     // 0: a path that ends with a shadow ray pending always waits one bounce for it
     int shade_partition = 0;             // 1: the shade step regroups a block's 128 entries into hits | misses (measured slower)
+    int tail_share = 1;                  // once the ray queue is drained, a warp's idle lanes take subtrees off its busy lanes' stacks:
+                                         // 0 never, 1 in launches with >= 4 rays per thread, 2 always
     int refill_below = 0;                // persistent traversal warps refill below this many live lanes (0: 24 / 20 by step)
     int fetch_chunk = 0;                 // >0: warp-private fetch chunks
     int profile_stages = 0;              // per-stage events, one pipeline, no graphs, no finish kernel

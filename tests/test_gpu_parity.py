@@ -220,8 +220,9 @@ def test_wavefront_equals_megakernel_and_sorting_is_neutral():
         films, counts = [], []
         try:
             for mode, sort, part in ((abi.MODE_WAVEFRONT, 1, 0), (abi.MODE_WAVEFRONT, 2, 0), (abi.MODE_WAVEFRONT, 0, 1),
-                                     (abi.MODE_WAVEFRONT, 0, 0), (abi.MODE_MEGAKERNEL, 0, 0)):
-                pkg.set_option("shade_partition", part)
+                                     (abi.MODE_WAVEFRONT, 0, 0), (abi.MODE_MEGAKERNEL, 0, 0), (abi.MODE_WAVEFRONT, 0, 2)):
+                pkg.set_option("shade_partition", part & 1)
+                pkg.set_option("tail_share", 0 if part == 2 else 2)  # idle lanes helping busy ones in a launch's tail: never / always
                 p = sc.integrator.params()
                 p.mode, p.sort_materials = mode, sort
                 film, st = be.render(p)
@@ -230,6 +231,7 @@ def test_wavefront_equals_megakernel_and_sorting_is_neutral():
                     counts.append((st.n_samples, st.n_closest_rays, st.n_shadow_rays))
         finally:
             pkg.set_option("shade_partition", 0)
+            pkg.set_option("tail_share", 1)
         assert all(same_bits(films[0], f) for f in films[1:])
         assert all(c == counts[0] for c in counts[1:])
         be.close()
@@ -450,3 +452,38 @@ def test_images_at_4096_spp_vs_reference():
         mean_ours, mean_ref = films["lcg"][..., :3].mean(), G[name + "_pcg"][..., :3].mean()
         assert abs(mean_ours - mean_ref) / mean_ref < 0.005, (name, mean_ours, mean_ref)
         be.close()
+
+
+def test_tail_share_is_neutral(G, S):
+    """Option tail_share: once a traversal launch's queue is drained, a warp's idle lanes take pending subtrees off its
+    busy lanes' stacks and traverse them for the same ray, handing their best hit back (kernels.cu tail_share). Forced
+    on for every launch (2) and off (0): hits, occlusion flags and films must be the same bits, and equal the goldens."""
+    rng = np.random.default_rng(17)
+    sc = scenes.terrain_scene(n=160, resolution=(64, 36), spp=1)
+    org, dr = random_rays(rng, 150000, (-50, -2, -50), (50, 15, 50))
+    dr[::2, 1] *= 0.02  # grazing rays: the long dependent chains the sharing is for
+    dra = dr.copy()
+    dra[:, 3] = 40.0
+    want = Oracle(sc).trace(org, dr)
+    want_occ = Oracle(sc).trace(org, dra, any_hit=True)
+    ml = scenes.many_light_scene(n=48, resolution=(64, 36), spp=8, max_depth=16, n_quads=500)
+    ml_ref = Oracle(ml).render(ml.integrator.params())
+    try:
+        for share in (2, 0):
+            pkg.set_option("tail_share", share)
+            be = backend(sc)
+            got = be.trace(org, dr)
+            assert hit_mismatch(want, got) == (0, 0, 0), share
+            assert np.array_equal(be.trace(org, dra, any_hit=True), want_occ), share
+            be.close()
+            be = backend(S["terrain"])
+            h = be.trace(G["terrain_org2"], G["terrain_dir2"])
+            assert hit_mismatch(G["terrain_hits2"], h) == (0, 0, 0)
+            assert np.array_equal(be.trace(G["terrain_org2"], G["terrain_dir2_any"], any_hit=True), G["terrain_occ2"])
+            assert n_diff_px(be.render(S["terrain"].integrator.params())[0], G["terrain_film"]) == 0
+            be.close()
+            be = backend(ml)
+            assert n_diff_px(be.render(ml.integrator.params())[0], ml_ref) == 0, share
+            be.close()
+    finally:
+        pkg.set_option("tail_share", 1)

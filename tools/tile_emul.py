@@ -39,6 +39,8 @@ def main():
         for _ in range(4):
             st = be.render_device(film.data_ptr(), p)
             best = min(best, st.ms_total)
+        if opts.get("profile_stages") == "1":
+            print("   stages: total %.2f extend %.2f shade %.2f ms, launches %d" % (st.ms_total, st.ms_extend, st.ms_shade, st.n_kernel_launches))
         h = int(torch.sum(film.view(torch.int32).long() & 0xFFFFF).item())
         out.append("rank %d: %.2f ms (%d launches, %d+%d rays, film-hash %d)" % (rank, best, st.n_kernel_launches, st.n_closest_rays, st.n_shadow_rays, h))
     ideal = None
