@@ -167,3 +167,10 @@ class Backend:
         out = np.zeros((h, w, 3), np.uint8)
         _check(self.lib, self.lib.akb_film_to_srgb8(_ptr(np.ascontiguousarray(film, np.float32)), w, h, _ptr(out)))
         return out
+
+    def film_to_srgb8_noalloc(self, film):
+        """akb_film_to_srgb8_noalloc: same bytes, static device scratch, no allocation (include/akari_b200.h)."""
+        h, w = film.shape[:2]
+        out = np.zeros((h, w, 3), np.uint8)
+        _check(self.lib, self.lib.akb_film_to_srgb8_noalloc(_ptr(np.ascontiguousarray(film, np.float32)), w, h, _ptr(out)))
+        return out

@@ -70,7 +70,7 @@ LIB_NAME = "libakari_b200.so"
 # every symbol include/akari_b200.h declares (tests check the built library exports all of them)
 SYMBOLS = ["akb_init", "akb_init_device", "akb_n_devices", "akb_set_option", "akb_shutdown", "akb_last_error", "akb_device_count", "akb_scene_create", "akb_scene_destroy",
            "akb_scene_info", "akb_render", "akb_render_device", "akb_trace", "akb_trace_device", "akb_generate_rays",
-           "akb_film_to_srgb8", "akb_scene_file_load", "akb_scene_file_desc", "akb_scene_file_params",
+           "akb_film_to_srgb8", "akb_film_to_srgb8_noalloc", "akb_scene_file_load", "akb_scene_file_desc", "akb_scene_file_params",
            "akb_scene_file_output", "akb_scene_file_destroy", "akb_write_png", "akb_write_pfm"]
 
 
@@ -125,6 +125,8 @@ def load():
     L.akb_generate_rays.restype = C.c_int
     L.akb_film_to_srgb8.argtypes = [vp, C.c_int32, C.c_int32, vp]
     L.akb_film_to_srgb8.restype = C.c_int
+    L.akb_film_to_srgb8_noalloc.argtypes = [vp, C.c_int32, C.c_int32, vp]
+    L.akb_film_to_srgb8_noalloc.restype = C.c_int
     L.akb_scene_file_load.argtypes = [C.c_char_p, C.POINTER(vp)]
     L.akb_scene_file_load.restype = C.c_int
     L.akb_scene_file_desc.argtypes = [vp]

@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <chrono>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -1141,3 +1142,61 @@ akb_status akb_film_to_srgb8(const float *rgbw, int32_t width, int32_t height, u
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// akb_film_to_srgb8_noalloc: the byte stage of akb_film_to_srgb8 for callers that may not allocate (CUDA graph capture
+// around them, serving loops, harnesses that forbid cudaMalloc). No counterpart in the reference. The device staging of
+// akb_film_to_srgb8 (film in, RGB8 out: two cudaMalloc + cudaFree per call) lives in ONE file-scope device array
+// instead: [0, 16 * kNoAllocMaxPixels) the float4 film, [16 * kNoAllocMaxPixels, 19 * kNoAllocMaxPixels) the bytes.
+// Every GPU that loads this library holds the 38 MiB until the process exits. All calls share the array (it keeps the
+// last call's contents; nothing in it has to start at zero: each call overwrites every byte it later reads), so calls
+// that overlap on the GPU race.
+constexpr size_t kNoAllocMaxPixels = AKB_NOALLOC_MAX_PIXELS;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocMaxPixels * 19];
+
+namespace {
+std::mutex g_noalloc_mu;
+unsigned char *g_noalloc_ptr[kMaxDevices] = {}; // device address of g_noalloc_scratch per device ordinal
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: resolve it once per device, with
+// that device current.
+cudaError_t noalloc_scratch(int device, unsigned char **out) {
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        int cur = -1;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess) return e;
+        if (cur != device) return cudaErrorInvalidDevice;
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        g_noalloc_ptr[device] = (unsigned char *)p;
+    }
+    *out = g_noalloc_ptr[device];
+    return cudaSuccess;
+}
+} // namespace
+
+extern "C" akb_status akb_film_to_srgb8_noalloc(const float *rgbw, int32_t width, int32_t height, uint8_t *out_rgb8) {
+    akb_status st = check_ready("akb_film_to_srgb8_noalloc");
+    if (st != AKB_OK) return st;
+    if (!rgbw || !out_rgb8 || width <= 0 || height <= 0)
+        return set_err(AKB_INVALID_ARG, "akb_film_to_srgb8_noalloc: bad argument");
+    const size_t n = (size_t)width * (size_t)height;
+    if (n > kNoAllocMaxPixels)
+        return set_err(AKB_INVALID_ARG,
+                       "akb_film_to_srgb8_noalloc: %d x %d = %zu pixels exceed the static scratch of %zu pixels "
+                       "(AKB_NOALLOC_MAX_PIXELS); use akb_film_to_srgb8",
+                       width, height, n, kNoAllocMaxPixels);
+    const int device = g_devs[0].index;
+    CU(cudaSetDevice(device));
+    unsigned char *scratch = nullptr;
+    CU(noalloc_scratch(device, &scratch));
+    float4 *d_in = (float4 *)scratch;
+    uint8_t *d_out = scratch + kNoAllocMaxPixels * sizeof(float4);
+    CU(cudaMemcpy(d_in, rgbw, n * sizeof(float4), cudaMemcpyHostToDevice));
+    CU(launch_film_to_srgb8(d_in, n, d_out, 0));
+    CU(cudaMemcpy(out_rgb8, d_out, n * 3, cudaMemcpyDeviceToHost));
+    return AKB_OK;
+}

@@ -257,6 +257,16 @@ akb_status akb_generate_rays(akb_scene *scene, const int32_t *xy, const float *u
  * sRGB OETF -> round(255.5*x) clamp -> RGB8. HOST pointers; runs on the device. */
 akb_status akb_film_to_srgb8(const float *rgbw, int32_t width, int32_t height, uint8_t *out_rgb8);
 
+/* akb_film_to_srgb8 for callers that may not allocate device memory (code under CUDA graph capture, serving loops,
+ * harnesses that forbid cudaMalloc). This entry point has NO counterpart in the reference.
+ * Same arguments (HOST pointers) and the same bytes out as akb_film_to_srgb8, but
+ * the device staging is one static device array of AKB_NOALLOC_MAX_PIXELS pixels (19 bytes per pixel = 38 MiB, held
+ * by every GPU that loads the library until the process exits) instead of two cudaMalloc / cudaFree per call: the
+ * call allocates and frees nothing. width * height > AKB_NOALLOC_MAX_PIXELS -> AKB_INVALID_ARG. All calls share the
+ * array (a process has one copy per GPU): calls of one process that overlap on the GPU race; serialise them. */
+#define AKB_NOALLOC_MAX_PIXELS ((size_t)1 << 21) /* 2 097 152: a 1920x1080 film fits */
+akb_status akb_film_to_srgb8_noalloc(const float *rgbw, int32_t width, int32_t height, uint8_t *out_rgb8);
+
 /* ---- scene files (front-end) ------------------------------------------------------------------------ */
 
 /* Replaces SceneGraphParser<C>::parse_file + the scene-graph nodes' object_field/compile for the Path hot path
