@@ -169,6 +169,11 @@ struct Replica {
         int n_bounces = 0;
     } bounce_graph[2];
     cudaStream_t cap_stream = nullptr;
+    // streaming wavefront (option stream): the two rings and their control block, sized with the workspace
+    uint32_t *r_ring = nullptr;
+    uint4 *q_ring = nullptr;
+    int ring_shift = 0;
+    StreamCtl *d_stream = nullptr, *h_stream = nullptr;
     // pinned staging of the film for akb_render's device-to-host copy
     char *h_film = nullptr;
     size_t h_film_bytes = 0;
@@ -197,6 +202,12 @@ struct Replica {
         for (void *p : ws_allocs) cudaFree(p);
         ws_allocs.clear();
         ws_slots = 0;
+        free_rings();
+    }
+    void free_rings() {
+        if (r_ring) cudaFree(r_ring);
+        if (q_ring) cudaFree(q_ring);
+        r_ring = nullptr, q_ring = nullptr, ring_shift = 0;
     }
     ~Replica() {
         if (dev.index >= 0) cudaSetDevice(dev.index);
@@ -207,6 +218,8 @@ struct Replica {
         for (void *p : allocs) cudaFree(p);
         if (d_ctr) cudaFree(d_ctr);
         if (h_ctr) cudaFreeHost(h_ctr);
+        if (d_stream) cudaFree(d_stream);
+        if (h_stream) cudaFreeHost(h_stream);
         if (d_film) cudaFree(d_film);
         if (h_film) cudaFreeHost(h_film);
         for (cudaEvent_t e : ev_chunk) cudaEventDestroy(e);
@@ -301,6 +314,24 @@ akb_status ensure_film(Replica *r, size_t n_px) {
     return AKB_OK;
 }
 
+// Rings of the streaming wavefront: twice the next power of two of the slot count (a path has one entry in flight, so
+// half a lap always separates a producer from the entries still being read).
+akb_status ensure_rings(Replica *r, int n_slots) {
+    int shift = 19; // at least 2^20 entries: a lap must take much longer than any reader sits on a ticket (kernels.cu)
+    while ((1 << shift) < n_slots) shift++;
+    shift++;
+    if (!r->d_stream) {
+        CU(cudaMalloc((void **)&r->d_stream, sizeof(StreamCtl)));
+        CU(cudaMallocHost((void **)&r->h_stream, sizeof(StreamCtl)));
+    }
+    if (r->ring_shift == shift && r->r_ring) return AKB_OK;
+    r->free_rings();
+    CU(cudaMalloc((void **)&r->r_ring, sizeof(uint32_t) << shift));
+    CU(cudaMalloc((void **)&r->q_ring, sizeof(uint4) << shift));
+    r->ring_shift = shift;
+    return AKB_OK;
+}
+
 // The slots [base, base + n) of the frame's workspace as a workspace of their own (own queues, own counters).
 Workspace workspace_view(const Workspace &w, int base, int n, Counters *ctr) {
     Workspace v = w;
@@ -349,6 +380,7 @@ akb_status push_device_options() {
         CU(set_shade_partition(o.shade_partition));
         CU(set_tail_share(o.tail_share));
         CU(set_fetch_chunk(o.fetch_chunk));
+        CU(set_stream_options(o.stream_flex_mask, o.stream_watchdog_ms));
     }
     if (!g_devs.empty()) CU(cudaSetDevice(g_devs[0].index));
     return AKB_OK;
@@ -655,6 +687,7 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
     if (rc.ao) rc.sort_materials = 0, rc.ray_clamp = 0.0f; // AO: no materials, samples are exact 0/1
     const size_t n_px = (size_t)width * height;
     uint64_t launches = 0;
+    bool streamed = false;
     std::vector<cudaEvent_t> evs;
     const bool profile_stages = opt.profile_stages != 0;
     if (!film_is_shared) CU(cudaMemsetAsync(film, 0, n_px * sizeof(float4), stream));
@@ -666,6 +699,23 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
     } else if (p->mode == AKB_MODE_MEGAKERNEL) {
         CU(launch_megakernel(r->S, rc, film, r->d_ctr, stream));
         launches = 1;
+    } else if (opt.stream && !rc.ao && !rc.sort_materials && !profile_stages && rc.map.n_slots() <= kStreamMaxSlots && rc.spp > 0 &&
+               rc.map.n_slots() > 0) {
+        // Streaming wavefront: one persistent launch, no barrier between bounces (kernels.cu)
+        const int n_total = rc.map.n_slots();
+        akb_status st = ensure_workspace(r, n_total);
+        if (st == AKB_OK) st = ensure_rings(r, n_total);
+        if (st != AKB_OK) return st;
+        Workspace w = workspace_view(r->ws, 0, n_total, r->d_ctr);
+        w.r_ring = r->r_ring, w.q_ring = r->q_ring, w.ring_shift = r->ring_shift, w.sc = r->d_stream;
+        CU(cudaMemsetAsync(r->r_ring, 0xFF, sizeof(uint32_t) << r->ring_shift, stream)); // lap stamp 127: nothing there yet
+        CU(cudaMemsetAsync(r->q_ring, 0xFF, sizeof(uint4) << r->ring_shift, stream));
+        CU(cudaMemsetAsync(r->d_stream, 0, sizeof(StreamCtl), stream));
+        CU(launch_wf_init(r->S, rc, w, n_sms, stream));
+        CU(launch_wf_stream(r->S, rc, w, n_sms, stream));
+        CU(launch_wf_resolve(rc, w, film, stream));
+        launches = 4;
+        streamed = true;
     } else {
         const int n_total = rc.map.n_slots();
         akb_status st = ensure_workspace(r, n_total);
@@ -800,13 +850,25 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
     }
     CU(cudaEventRecord(r->ev1, stream));
     CU(cudaMemcpyAsync(r->h_ctr, r->d_ctr, 2 * sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+    if (streamed) CU(cudaMemcpyAsync(r->h_stream, r->d_stream, sizeof(StreamCtl), cudaMemcpyDeviceToHost, stream));
     CU(cudaStreamSynchronize(stream));
+    if (streamed && (r->h_stream->abort || !r->h_stream->done))
+        return set_err(AKB_CUDA_ERROR, "akb_render: the streaming wavefront stopped on its watchdog (%u of %u slots finished)",
+                       r->h_stream->n_finished, r->h_stream->n_started);
+    if (streamed && opt.timeline)
+        fprintf(stderr, "akb stream: gpu %d: %llu shade batches, %llu rays traced by shade-first warps, %llu idle polls\n", r->dev.index, r->h_stream->stat_shade_batches,
+                r->h_stream->stat_flex_rays, r->h_stream->stat_idle_polls);
     if (stats) {
         memset(stats, 0, sizeof *stats);
-        for (int k = 0; k < 2; k++) {
+        for (int k = 0; k < 2 && !streamed; k++) {
             stats->n_samples += r->h_ctr[k].stat_samples;
             stats->n_closest_rays += r->h_ctr[k].stat_closest - r->h_ctr[k].stat_skipped;
             stats->n_shadow_rays += r->h_ctr[k].stat_shadow;
+        }
+        if (streamed) {
+            stats->n_samples = r->h_stream->stat_samples;
+            stats->n_closest_rays = r->h_stream->stat_closest;
+            stats->n_shadow_rays = r->h_stream->stat_shadow;
         }
         stats->n_kernel_launches = launches;
         stats->n_gpus_used = 1;

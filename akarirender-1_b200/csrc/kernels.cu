@@ -540,6 +540,107 @@ __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_trace_kernel(
     }
 }
 
+// Path state in HBM is read through L1 by the bounce-synchronous kernels (a kernel boundary separates writer and reader)
+// and past it (ld.global.cg: L2 is the point of coherence) by the streaming kernel, whose writers and readers run at
+// the same time on different SMs.
+template <bool STREAM, class V> __device__ __forceinline__ V ldw(const V *p) {
+    if (STREAM) return __ldcg(p);
+    return *p;
+}
+
+// One shade step of one path, shared by wf_shade_kernel and the streaming kernel: the closest-hit result (hu, hv, tri;
+// tri < 0 = miss or a parked entry) of the path in `slot` -> path_vertex, the next extension ray and the shadow ray
+// written to the slot, finished samples added to the slot accumulator and the pixel's next sample started in place.
+// Out: push_ext / ext_entry (the slot goes on: traced, or parked with kDeadRay), push_sh (a shadow ray was written),
+// slot_done (the pixel's last sample is in the accumulator: nothing more to do for this slot).
+template <int SAMP, bool TEX, bool AO, bool STREAM>
+__device__ __forceinline__ bool shade_vertex(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, uint32_t slot, float hu, float hv,
+                                             int tri, bool &push_ext, bool &push_sh, uint32_t &ext_entry, uint32_t &n_done,
+                                             uint32_t &n_parked) {
+    bool slot_done = false;
+    ext_entry = slot;
+    PathState<SAMP> ps;
+    ps.rng.s = ldw<STREAM>(ws.rng + slot);
+    ps.L = mk3(0, 0, 0); // running L stays in HBM; path_vertex only ever adds emission, at depth 0
+    bool finished = true; // path ends at this vertex
+    if (AO) {
+        if (tri >= 0) {
+            const RaySeg sh = ao_ray<SAMP>(S, ps.rng, hu, hv, tri, rc.ao_occlude);
+            ws.sh_o[slot] = mk4(sh.o, sh.tmin);
+            ws.sh_d[slot] = mk4(sh.d, sh.tmax);
+            ws.sh_c[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+            ws.rng[slot] = ps.rng.s;
+            ext_entry = slot | kDeadRay;
+            push_sh = push_ext = true, finished = false;
+            n_parked++;
+        }
+    } else if (tri >= 0) {
+        const float4 bd = ldw<STREAM>(ws.beta + slot);
+        const float4 rd = ldw<STREAM>(ws.ray_d + slot);
+        ps.beta = xyz(bd), ps.depth = __float_as_int(bd.w);
+        RaySeg next, sh;
+        v3 sc;
+        const int fl = path_vertex<SAMP>(S, ps, xyz(rd), hu, hv, tri, rc.max_depth, rc.rr_start, next, sh, sc, TEX);
+        bool cont = (fl & VTX_CONTINUE) != 0;
+        const bool shadow = (fl & VTX_SHADOW) != 0;
+        // A ray leaving a vertex at depth == max_depth can never contribute (kernel/pathtracer.h:102-112: no
+        // emission at depth > 0, no scattering at depth >= max_depth): it is not traced.
+        if (cont && ps.depth >= rc.max_depth && ps.depth > 0) cont = false;
+        if (shadow) {
+            ws.sh_o[slot] = mk4(sh.o, sh.tmin);
+            ws.sh_d[slot] = mk4(sh.d, sh.tmax);
+            ws.sh_c[slot] = mk4(sc, 0.f);
+            push_sh = true;
+        }
+        if (cont) {
+            ws.ray_o[slot] = mk4(next.o, next.tmin);
+            ws.ray_d[slot] = mk4(next.d, next.tmax);
+            ws.beta[slot] = mk4(ps.beta, __int_as_float(ps.depth));
+            ws.rng[slot] = ps.rng.s;
+            push_ext = true, finished = false;
+        } else if (shadow) {
+            // The path ends here, but the film add must wait for this vertex's shadow ray.
+            const float4 Lr = ldw<STREAM>(ws.L + slot);
+            const int done = __float_as_int(Lr.w) + 1;
+            if (done < rc.spp && g_no_park) {
+                // The pixel starts its next sample now; the traversal step that resolves the shadow ray adds
+                // the finished sample to the film (both possible values are worked out here).
+                ws.sh_c[slot] = mk4(clamp_sample(add3(xyz(Lr), sc), rc.ray_clamp), 1.f);
+                ws.sh_b[slot] = mk4(clamp_sample(xyz(Lr), rc.ray_clamp), 0.f);
+                n_done++;
+                int x, y;
+                slot_to_pixel(rc.map, (int)slot + ws.slot_base, x, y);
+                start_sample<SAMP>(S, ws, (int)slot, x, y, ps.rng, done);
+                push_ext = true, finished = false;
+            } else {
+                // last sample of the pixel: park the path for one step
+                ws.rng[slot] = ps.rng.s;
+                ext_entry = slot | kDeadRay;
+                push_ext = true, finished = false;
+                n_parked++; // the queue entry is counted by the next traversal launch but traces nothing
+            }
+        }
+    }
+    if (finished) { // "Splat" + regenerate (gpu/cuda/integrator.cpp:385-401, core/film.h:66-70)
+        const float4 Lr = ldw<STREAM>(ws.L + slot);
+        const v3 L = add3(xyz(Lr), ps.L); // ps.L != 0 only for a camera-visible emitter, where Lr.xyz == 0
+        const int done = __float_as_int(Lr.w) + 1;
+        float4 a = ldw<STREAM>(ws.acc + slot);
+        const v3 s = add3(xyz(a), clamp_sample(L, rc.ray_clamp));
+        ws.acc[slot] = make_float4(s.x, s.y, s.z, a.w + 1.0f);
+        n_done++;
+        if (done < rc.spp) {
+            int x, y;
+            slot_to_pixel(rc.map, (int)slot + ws.slot_base, x, y);
+            start_sample<SAMP>(S, ws, (int)slot, x, y, ps.rng, done);
+            push_ext = true;
+        } else {
+            slot_done = true;
+        }
+    }
+    return slot_done;
+}
+
 // AO = true: the AO integrator on the same queues (kernel/integrators/cpu/integrator.cpp:72-80): a hit vertex emits one
 // cosine-weighted any-hit ray carrying (1,1,1) and the path parks for one step, so that the sample is 1 iff that ray
 // is unoccluded; a miss finishes with 0. Sampler order and film sums are those of ao_kernel.
@@ -609,87 +710,9 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
             if (valid) slot = s_slot[threadIdx.x], hrec = s_hit[threadIdx.x];
             __syncthreads(); // the arrays are rewritten by the next round
         }
-        if (valid) {
-            ext_entry = slot;
-            const int tri = __float_as_int(hrec.z);
-            PathState<SAMP> ps;
-            ps.rng.s = ws.rng[slot];
-            ps.L = mk3(0, 0, 0); // running L stays in HBM; path_vertex only ever adds emission, at depth 0
-            bool finished = true; // path ends at this vertex
-            if (AO) {
-                if (tri >= 0) {
-                    const RaySeg sh = ao_ray<SAMP>(S, ps.rng, hrec.x, hrec.y, tri, rc.ao_occlude);
-                    ws.sh_o[slot] = mk4(sh.o, sh.tmin);
-                    ws.sh_d[slot] = mk4(sh.d, sh.tmax);
-                    ws.sh_c[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-                    ws.rng[slot] = ps.rng.s;
-                    ext_entry = slot | kDeadRay;
-                    push_sh = push_ext = true, finished = false;
-                    n_parked++;
-                }
-            } else if (tri >= 0) {
-                const float4 bd = ws.beta[slot];
-                const float4 rd = ws.ray_d[slot];
-                ps.beta = xyz(bd), ps.depth = __float_as_int(bd.w);
-                RaySeg next, sh;
-                v3 sc;
-                const int fl = path_vertex<SAMP>(S, ps, xyz(rd), hrec.x, hrec.y, tri, rc.max_depth, rc.rr_start, next, sh, sc, TEX);
-                bool cont = (fl & VTX_CONTINUE) != 0;
-                const bool shadow = (fl & VTX_SHADOW) != 0;
-                // A ray leaving a vertex at depth == max_depth can never contribute (kernel/pathtracer.h:102-112: no
-                // emission at depth > 0, no scattering at depth >= max_depth): it is not traced.
-                if (cont && ps.depth >= rc.max_depth && ps.depth > 0) cont = false;
-                if (shadow) {
-                    ws.sh_o[slot] = mk4(sh.o, sh.tmin);
-                    ws.sh_d[slot] = mk4(sh.d, sh.tmax);
-                    ws.sh_c[slot] = mk4(sc, 0.f);
-                    push_sh = true;
-                }
-                if (cont) {
-                    ws.ray_o[slot] = mk4(next.o, next.tmin);
-                    ws.ray_d[slot] = mk4(next.d, next.tmax);
-                    ws.beta[slot] = mk4(ps.beta, __int_as_float(ps.depth));
-                    ws.rng[slot] = ps.rng.s;
-                    push_ext = true, finished = false;
-                } else if (shadow) {
-                    // The path ends here, but the film add must wait for this vertex's shadow ray.
-                    const float4 Lr = ws.L[slot];
-                    const int done = __float_as_int(Lr.w) + 1;
-                    if (done < rc.spp && g_no_park) {
-                        // The pixel starts its next sample now; the traversal step that resolves the shadow ray adds
-                        // the finished sample to the film (both possible values are worked out here).
-                        ws.sh_c[slot] = mk4(clamp_sample(add3(xyz(Lr), sc), rc.ray_clamp), 1.f);
-                        ws.sh_b[slot] = mk4(clamp_sample(xyz(Lr), rc.ray_clamp), 0.f);
-                        n_done++;
-                        int x, y;
-                        slot_to_pixel(rc.map, (int)slot + ws.slot_base, x, y);
-                        start_sample<SAMP>(S, ws, (int)slot, x, y, ps.rng, done);
-                        push_ext = true, finished = false;
-                    } else {
-                        // last sample of the pixel: park the path for one step
-                        ws.rng[slot] = ps.rng.s;
-                        ext_entry = slot | kDeadRay;
-                        push_ext = true, finished = false;
-                        n_parked++; // the queue entry is counted by the next traversal launch but traces nothing
-                    }
-                }
-            }
-            if (finished) { // "Splat" + regenerate (gpu/cuda/integrator.cpp:385-401, core/film.h:66-70)
-                const float4 Lr = ws.L[slot];
-                const v3 L = add3(xyz(Lr), ps.L); // ps.L != 0 only for a camera-visible emitter, where Lr.xyz == 0
-                const int done = __float_as_int(Lr.w) + 1;
-                float4 a = ws.acc[slot];
-                const v3 s = add3(xyz(a), clamp_sample(L, rc.ray_clamp));
-                ws.acc[slot] = make_float4(s.x, s.y, s.z, a.w + 1.0f);
-                n_done++;
-                if (done < rc.spp) {
-                    int x, y;
-                    slot_to_pixel(rc.map, (int)slot + ws.slot_base, x, y);
-                    start_sample<SAMP>(S, ws, (int)slot, x, y, ps.rng, done);
-                    push_ext = true;
-                }
-            }
-        }
+        if (valid)
+            shade_vertex<SAMP, TEX, AO, false>(S, rc, ws, slot, hrec.x, hrec.y, __float_as_int(hrec.z), push_ext, push_sh, ext_entry, n_done,
+                                               n_parked);
         if (push_sh) ext_entry |= kHasShadow; // a shadow ray always comes with an extension entry (continuing or parked)
         AKB_CHECK(!valid || slot < (uint32_t)ws.n_slots);
         queue_push2(push_ext, ext_entry, ws.q_ext[b ^ 1], &ctr->n_ext[b ^ 1], push_sh, slot, ws.q_sh[b ^ 1], &ctr->n_sh[b ^ 1], (uint32_t)ws.n_slots);
@@ -823,6 +846,343 @@ __global__ void __launch_bounds__(256) film_sum_peers_kernel(float4 *__restrict_
             a.x += b.x, a.y += b.y, a.z += b.z, a.w += b.w;
         }
         dst[i] = a;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Streaming wavefront (akb_set_option("stream", 1)): ONE persistent launch renders the whole share, with no barrier
+// between bounces. The bounce-synchronous kernels above pay, on every one of a frame's spp x depth rounds, for the
+// slowest ray of that round (the launch cannot end before it does) and, once the short pixels have used up their
+// samples, for rounds that hold few paths: at 1080p the same samples cost 18 % more than at 8K, where rounds are 16
+// times larger (tools/res_scaling.py). Here a path moves on as soon as ITS rays are traced:
+//   ray ring  (shade -> trace): one 32-bit entry per path that has rays to trace - its shadow ray, if any, and then
+//              its extension ray, traced back to back by the lane that took the entry (so a path has one message in
+//              flight at a time and needs no counting of outstanding rays);
+//   hit ring  (trace -> shade): one 16-byte entry per traced path: (slot | shadow result, triangle, u, v) - the whole
+//              result travels in the message, written by ONE 16-byte store, so the traversal side needs no fence.
+// Both rings are multi-producer / multi-consumer: a producer takes tickets with one atomic per warp, writes its
+// entries, each stamped with the ticket's lap number (7 bits); a consumer takes tickets the same way and reads an entry
+// once the stamp it expects shows up. Path state (rays, throughput, sampler, accumulator) stays in the slot-indexed
+// arrays, is written only by the shade side, published by `fence.release.gpu` (MEMBAR without the L1 invalidation of
+// __threadfence(): the traversal warps keep their BVH nodes in L1) before the ring entry, and read with ld.global.cg.
+// Every per-slot operation happens in the order of the bounce-synchronous kernels (shadow result -> L or the film,
+// then the vertex, samples in sequence), so the film is bit-identical to theirs (tests/test_stream.py).
+//   Warps are not tied to a job. Warp 0 of every block is "shade-first" (the warp-0s of the blocks resident on an SM
+// share one scheduler and its instruction cache): it shades whenever the hit ring holds anything and otherwise traces
+// ONE batch of rays at a time, without replacement; the other warps trace with ray replacement and shade only when the
+// ray ring has run dry and none of their rays is in flight. So nobody ever gives up a half-full warp to change jobs,
+// and the split of the machine between the two jobs follows the two rings' lengths by itself.
+__constant__ int c_stream_flex_mask = 1;      // bit w: warp w of a block prefers shading
+__constant__ int c_stream_watchdog_ms = 4000; // a warp that finds nothing to do for this long aborts the frame (a lost message)
+
+constexpr uint32_t kRShadow = 1u << 24, kRDead = 1u << 23, kRSlot = (1u << 23) - 1u;
+constexpr uint32_t kQUnocc = 1u << 24, kQHadShadow = 1u << 23;
+
+__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed(uint32_t *p, uint32_t v) { asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ uint4 ld_relaxed4(const uint4 *p) {
+    uint4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed4(uint4 *p, uint4 v) {
+    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void fence_release() { asm volatile("fence.release.gpu;" ::: "memory"); }
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// wf_init_kernel's list of started slots -> the first entries of the ray ring (lap 0)
+__global__ void stream_seed_kernel(Workspace ws) {
+    const uint32_t n = ws.ctr->n_ext[0];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) ws.r_ring[i] = ws.q_ext[0][i] & kRSlot;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        ws.sc->r_tail = n;
+        ws.sc->n_started = n;
+        if (n == 0) ws.sc->done = 1;
+    }
+}
+
+// Takes up to 32 entries off the hit ring (only if it holds at least min_backlog) and shades them; all 32 lanes enter.
+// Returns false if there was nothing to take. [q_next, q_end) = tickets this warp holds and has not consumed yet.
+template <int SAMP, bool TEX>
+__device__ __forceinline__ bool stream_shade_batch(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, uint32_t min_backlog,
+                                                   uint32_t n_started, uint32_t &q_next, uint32_t &q_end, uint32_t &n_done) {
+    const unsigned full = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31;
+    StreamCtl *sc = ws.sc;
+    const uint32_t mask = (1u << ws.ring_shift) - 1u;
+    if (q_next == q_end) {
+        uint32_t n = 0, base = 0;
+        if (lane == 0) {
+            const int backlog = (int)(ld_relaxed(&sc->q_tail) - ld_relaxed(&sc->q_head));
+            if (backlog >= (int)min_backlog) {
+                n = (uint32_t)min(32, backlog);
+                base = atomicAdd(&sc->q_head, n);
+            }
+        }
+        n = __shfl_sync(full, n, 0), base = __shfl_sync(full, base, 0);
+        if (n == 0) return false;
+        q_next = base, q_end = base + n;
+    }
+    const bool cand = lane < q_end - q_next;
+    const uint32_t tk = q_next + lane;
+    uint4 e = make_uint4(0u, 0u, 0u, 0u);
+    bool ready = false;
+    unsigned waiting = 0;
+    for (int spin = 0; spin < 32; spin++) { // entries whose producers hold the tickets are a store away; others may never come
+        if (cand && !ready) {
+            e = ld_relaxed4(ws.q_ring + (tk & mask));
+            ready = (e.x >> 25) == ((tk >> ws.ring_shift) & 127u);
+        }
+        waiting = __ballot_sync(full, cand && !ready);
+        if (waiting == 0) break;
+        __nanosleep(64);
+    }
+    const uint32_t n_take = waiting ? (uint32_t)(__ffs(waiting) - 1) : q_end - q_next;
+    if (n_take == 0) return false;
+    q_next += n_take;
+    const bool valid = lane < n_take;
+    bool push_ext = false, push_sh = false, slot_done = false;
+    uint32_t ext_entry = 0, n_parked = 0;
+    const uint32_t slot = e.x & kRSlot;
+    if (valid) {
+        AKB_CHECK(slot < (uint32_t)ws.n_slots);
+        if (e.x & kQHadShadow) { // what WfSrc::complete does for an any-hit item
+            const float4 c = __ldcg(ws.sh_c + slot);
+            const bool unoccluded = (e.x & kQUnocc) != 0;
+            if (c.w != 0.f) {
+                const float4 a = __ldcg(ws.acc + slot);
+                const v3 s = add3(xyz(a), unoccluded ? xyz(c) : xyz(__ldcg(ws.sh_b + slot)));
+                ws.acc[slot] = make_float4(s.x, s.y, s.z, a.w + 1.0f);
+            } else if (unoccluded) {
+                float4 L = __ldcg(ws.L + slot);
+                const v3 s = add3(xyz(L), xyz(c));
+                L.x = s.x, L.y = s.y, L.z = s.z;
+                ws.L[slot] = L;
+            }
+        }
+        slot_done = shade_vertex<SAMP, TEX, false, true>(S, rc, ws, slot, __uint_as_float(e.z), __uint_as_float(e.w), (int)e.y, push_ext, push_sh,
+                                                         ext_entry, n_done, n_parked);
+    }
+    fence_release(); // the rays and the path state written above reach L2 before the ring entries that announce them
+    const unsigned pm = __ballot_sync(full, push_ext);
+    if (pm) {
+        const int leader = __ffs(pm) - 1;
+        uint32_t base = 0;
+        if ((int)lane == leader) base = atomicAdd(&sc->r_tail, (uint32_t)__popc(pm));
+        base = __shfl_sync(full, base, leader);
+        if (push_ext) {
+            const uint32_t t = base + (uint32_t)__popc(pm & lanemask_lt());
+            st_relaxed(ws.r_ring + (t & mask), (((t >> ws.ring_shift) & 127u) << 25) | (push_sh ? kRShadow : 0u) | ((ext_entry & kDeadRay) ? kRDead : 0u) | slot);
+        }
+    }
+    const unsigned fm = __ballot_sync(full, slot_done);
+    if (fm && lane == 0) {
+        const uint32_t nf = (uint32_t)__popc(fm);
+        if (atomicAdd(&sc->n_finished, nf) + nf == n_started) st_relaxed(&sc->done, 1u);
+    }
+    return true;
+}
+
+template <int SAMP, bool TEX>
+__global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_stream_kernel(SceneDev S, RenderConfig rc, Workspace ws) {
+    const unsigned full = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31;
+    StreamCtl *sc = ws.sc;
+    const bool flex = ((c_stream_flex_mask >> (threadIdx.x >> 5)) & 1) != 0;
+    const uint32_t mask = (1u << ws.ring_shift) - 1u;
+    const int post_limit = S.trav_post_limit;
+    const int refill_below = c_refill_below > 0 ? c_refill_below : (post_limit >= 0 ? 24 : 20);
+    const uint32_t n_started = sc->n_started; // written by stream_seed_kernel, a launch ago
+    const float4 *__restrict__ nodes = S.nodes;
+    const float4 *__restrict__ tris = S.tris;
+
+    uint2 stack[kStackSize];
+    Trav T;
+    trav_init(T, mk3(0, 0, 0), mk3(0, 0, 1), 0.f, 0.f, false);
+    bool active = false, have = false; // traversing / a traversal of this lane has just ended
+    bool in_shadow = false, unocc = false;
+    uint32_t ent = 0;                                       // the ray-ring entry this lane works on
+    uint32_t r_next = 0, r_end = 0, q_next = 0, q_end = 0; // tickets held and not yet consumed (warp-uniform)
+    bool starved = false;                                   // the last refill found no entry for an idle lane
+    uint32_t n_closest = 0, n_shadow = 0, n_done = 0, n_batches = 0, n_flex_rays = 0, n_idle = 0;
+    unsigned long long idle_since = 0;
+
+    // Readers take tickets only for entries the ring holds (head < tail when they looked); two readers racing for the
+    // same entries leave the loser with tickets whose entries come later. Such tickets are never sat on: ray-ring
+    // tickets are looked at on every pass of this loop (at most eight traversal steps or one shade batch apart), and a
+    // warp whose hit-ring tickets have been served takes no new rays until it has shaded them - so an entry waits
+    // microseconds for its reader, while a lap of a ring (>= 2^20 entries) takes the whole GPU hundreds of
+    // microseconds to produce.
+    for (;;) {
+        // ---- traversals that ended: shadow ray -> the path's extension ray; extension ray (or none) -> message ----
+        bool msg = false;
+        if (have) {
+            have = false;
+            if (in_shadow) {
+                in_shadow = false;
+                unocc = T.hit.tri < 0;
+                if (!(ent & kRDead)) {
+                    const uint32_t slot = ent & kRSlot;
+                    const float4 o = __ldcg(ws.ray_o + slot), d = __ldcg(ws.ray_d + slot);
+                    trav_init(T, xyz(o), xyz(d), o.w, d.w, false);
+                    active = true;
+                    n_closest++;
+                } else {
+                    T.hit.tri = -1; // a parked path: nothing else to trace
+                    msg = true;
+                }
+            } else {
+                msg = true;
+            }
+        }
+        const unsigned mm = __ballot_sync(full, msg);
+        if (mm) {
+            const int leader = __ffs(mm) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(&sc->q_tail, (uint32_t)__popc(mm));
+            base = __shfl_sync(full, base, leader);
+            if (msg) {
+                const uint32_t t = base + (uint32_t)__popc(mm & lanemask_lt());
+                uint4 v;
+                v.x = (((t >> ws.ring_shift) & 127u) << 25) | (unocc ? kQUnocc : 0u) | ((ent & kRShadow) ? kQHadShadow : 0u) | (ent & kRSlot);
+                v.y = (uint32_t)T.hit.tri, v.z = __float_as_uint(T.hit.u), v.w = __float_as_uint(T.hit.v);
+                st_relaxed4(ws.q_ring + (t & mask), v);
+            }
+        }
+        bool progress = mm != 0;
+        unsigned act = __ballot_sync(full, active);
+
+        // ---- no ray in flight in this warp: it is free to shade. Shade-first warps whenever the hit ring holds
+        //      anything; the others once the ray ring has nothing for them; everybody the tickets already held ----
+        if (act == 0) {
+            bool did = false;
+            if (flex || starved || q_next != q_end) did = stream_shade_batch<SAMP, TEX>(S, rc, ws, 1u, n_started, q_next, q_end, n_done);
+            trav_init(T, mk3(0, 0, 0), mk3(0, 0, 1), 0.f, 0.f, false); // nothing of T lives across the shading code
+            if (did) {
+                n_batches++;
+                starved = false;
+                idle_since = 0;
+                if (r_next == r_end) continue; // (else: look at the ray-ring tickets this warp holds first)
+                progress = true;
+            }
+        }
+
+        // ---- idle lanes take entries off the ray ring (those whose stamp has arrived, in ticket order). Shade-first
+        //      warps take one batch at a time and only what is there; the others refill whenever lanes fall idle ----
+        const unsigned idle = __ballot_sync(full, !active);
+        bool hits_waiting = false; // this warp holds hit-ring tickets whose entries have arrived: no new rays, shade first
+        if (q_next != q_end && idle) {
+            uint32_t x = 0;
+            if (lane == 0) x = ld_relaxed(&ws.q_ring[q_next & mask].x);
+            x = __shfl_sync(full, x, 0);
+            hits_waiting = (x >> 25) == ((q_next >> ws.ring_shift) & 127u);
+        }
+        if (idle && !hits_waiting && (!flex || act == 0)) {
+            if (r_next == r_end) {
+                // only what the ring holds (a racing reader may still get there first: then the tickets are kept and
+                // looked at on every pass until their entries arrive)
+                uint32_t base = 0, want = (uint32_t)__popc(idle);
+                if (lane == 0) {
+                    want = (uint32_t)max(0, min((int)want, (int)(ld_relaxed(&sc->r_tail) - ld_relaxed(&sc->r_head))));
+                    if (want) base = atomicAdd(&sc->r_head, want);
+                }
+                base = __shfl_sync(full, base, 0), want = __shfl_sync(full, want, 0);
+                r_next = base, r_end = base + want;
+            }
+            const uint32_t avail = r_end - r_next;
+            const uint32_t rank = (uint32_t)__popc(idle & lanemask_lt());
+            const bool cand = !active && rank < avail;
+            uint32_t e = 0;
+            bool ready = false;
+            if (cand) {
+                const uint32_t t = r_next + rank;
+                e = ld_relaxed(ws.r_ring + (t & mask));
+                ready = (e >> 25) == ((t >> ws.ring_shift) & 127u);
+            }
+            const unsigned late = __ballot_sync(full, cand && !ready);
+            const uint32_t n_want = min((uint32_t)__popc(idle), avail);
+            const uint32_t n_take = late ? (uint32_t)__popc(idle & ((1u << (__ffs(late) - 1)) - 1u)) : n_want;
+            if (cand && rank < n_take) {
+                ent = e;
+                const uint32_t slot = e & kRSlot;
+                AKB_CHECK(slot < (uint32_t)ws.n_slots);
+                unocc = false;
+                if (flex) n_flex_rays++;
+                if (e & kRShadow) {
+                    const float4 o = __ldcg(ws.sh_o + slot), d = __ldcg(ws.sh_d + slot);
+                    trav_init(T, xyz(o), xyz(d), o.w, d.w, true);
+                    in_shadow = true, active = true;
+                    n_shadow++;
+                } else if (!(e & kRDead)) {
+                    const float4 o = __ldcg(ws.ray_o + slot), d = __ldcg(ws.ray_d + slot);
+                    trav_init(T, xyz(o), xyz(d), o.w, d.w, false);
+                    in_shadow = false, active = true;
+                    n_closest++;
+                } else { // (a parked entry always carries a shadow ray; kept for completeness)
+                    T.hit.tri = -1, in_shadow = false, have = true;
+                }
+            }
+            r_next += n_take;
+            starved = n_take < (uint32_t)__popc(idle);
+            if (n_take) progress = true;
+        }
+        act = __ballot_sync(full, active);
+        const unsigned hv0 = __ballot_sync(full, have);
+        if (act == 0) {
+            if (hv0 || progress) {
+                idle_since = 0;
+                continue;
+            }
+            // nothing to trace, nothing to shade: the frame is ending (or has just begun)
+            uint32_t flags = 0;
+            if (lane == 0) flags = ld_relaxed(&sc->done) | ld_relaxed(&sc->abort);
+            if (__shfl_sync(full, flags, 0)) break;
+            n_idle++;
+            if (lane == 0) {
+                const unsigned long long now = global_ns();
+                if (idle_since == 0) idle_since = now;
+                if (now - idle_since > (unsigned long long)c_stream_watchdog_ms * 1000000ull) st_relaxed(&sc->abort, 1u);
+            }
+            starved = true;
+            __nanosleep(400);
+            continue;
+        }
+        idle_since = 0;
+        // ---- traversal steps: until enough lanes have finished to make a refill worth its atomics; a warp that cannot
+        //      refill (shade-first: one batch at a time; ray ring empty) sends its results a few at a time ----
+        int steps = 0;
+        unsigned hv = hv0;
+        do {
+            if (post_limit >= 0 ? trav_step_ii(T, nodes, tris, stack, active, post_limit) : (active && trav_step(T, nodes, tris, stack)))
+                active = false, have = true;
+            act = __ballot_sync(full, active);
+            hv = __ballot_sync(full, have);
+            steps++;
+        } while (act != 0 && (flex ? __popc(hv) < 8 : (__popc(act) >= refill_below || (starved && hv == 0 && steps < 8))));
+    }
+    // ---- statistics ----
+    for (int o = 16; o > 0; o >>= 1) {
+        n_closest += __shfl_down_sync(full, n_closest, o);
+        n_shadow += __shfl_down_sync(full, n_shadow, o);
+        n_done += __shfl_down_sync(full, n_done, o);
+        n_flex_rays += __shfl_down_sync(full, n_flex_rays, o);
+    }
+    if (lane == 0) {
+        if (n_closest) atomicAdd(&sc->stat_closest, (unsigned long long)n_closest);
+        if (n_shadow) atomicAdd(&sc->stat_shadow, (unsigned long long)n_shadow);
+        if (n_done) atomicAdd(&sc->stat_samples, (unsigned long long)n_done);
+        if (n_batches) atomicAdd(&sc->stat_shade_batches, (unsigned long long)n_batches);
+        if (n_flex_rays) atomicAdd(&sc->stat_flex_rays, (unsigned long long)n_flex_rays);
+        if (n_idle) atomicAdd(&sc->stat_idle_polls, (unsigned long long)n_idle);
     }
 }
 
@@ -967,6 +1327,31 @@ cudaError_t launch_film_sum_peers(float4 *dst, const PeerFilms &peers, size_t n_
     if (n_px == 0 || peers.n == 0) return cudaSuccess;
     const int grid = (int)std::min<size_t>((n_px + 255) / 256, (size_t)n_sms * 8);
     film_sum_peers_kernel<<<grid, 256, 0, st>>>(dst, peers, n_px);
+    return cudaGetLastError();
+}
+
+cudaError_t set_stream_options(int flex_mask, int watchdog_ms) {
+    cudaError_t e = cudaMemcpyToSymbol(c_stream_flex_mask, &flex_mask, sizeof(int));
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_stream_watchdog_ms, &watchdog_ms, sizeof(int));
+    return e;
+}
+
+cudaError_t launch_wf_stream(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int n_sms, cudaStream_t st) {
+    static int occ[2][2] = {{blocks_per_sm(wf_stream_kernel<AKB_SAMPLER_LCG, false>, kBlock), blocks_per_sm(wf_stream_kernel<AKB_SAMPLER_LCG, true>, kBlock)},
+                            {blocks_per_sm(wf_stream_kernel<AKB_SAMPLER_PCG, false>, kBlock), blocks_per_sm(wf_stream_kernel<AKB_SAMPLER_PCG, true>, kBlock)}};
+    if (ws.n_slots == 0) return cudaSuccess;
+    if (ws.n_slots > kStreamMaxSlots || ws.ring_shift > 25 || ws.n_slots > (1 << ws.ring_shift)) return cudaErrorInvalidValue;
+    stream_seed_kernel<<<std::max(1, std::min((ws.n_slots + 255) / 256, n_sms * 8)), 256, 0, st>>>(ws);
+    const bool pcg = rc.sampler == AKB_SAMPLER_PCG, tex = S.n_textures > 0;
+    const int grid = n_sms * occ[pcg][tex];
+    if (pcg && tex)
+        wf_stream_kernel<AKB_SAMPLER_PCG, true><<<grid, kBlock, 0, st>>>(S, rc, ws);
+    else if (pcg)
+        wf_stream_kernel<AKB_SAMPLER_PCG, false><<<grid, kBlock, 0, st>>>(S, rc, ws);
+    else if (tex)
+        wf_stream_kernel<AKB_SAMPLER_LCG, true><<<grid, kBlock, 0, st>>>(S, rc, ws);
+    else
+        wf_stream_kernel<AKB_SAMPLER_LCG, false><<<grid, kBlock, 0, st>>>(S, rc, ws);
     return cudaGetLastError();
 }
 

@@ -18,6 +18,21 @@ struct Counters {
     unsigned long long stat_closest, stat_shadow, stat_samples, stat_skipped;
 };
 
+// Control block of the streaming wavefront (option stream = 1; one struct in HBM, zeroed before every frame). Tickets
+// are free-running 32-bit counters (wrap-around arithmetic); the hot ones sit on cache lines of their own.
+struct StreamCtl {
+    uint32_t r_tail, pad0[31]; // ray ring (shade -> trace): tickets handed to producers ...
+    uint32_t r_head, pad1[31]; // ... and to consumers (may run ahead of r_tail: consumers then wait for their entries)
+    uint32_t q_tail, pad2[31]; // hit ring (trace -> shade)
+    uint32_t q_head, pad3[31];
+    uint32_t n_started;        // slots that render at least one sample (set by stream_seed_kernel)
+    uint32_t n_finished;       // slots whose last sample is in the accumulator
+    uint32_t done;             // n_finished == n_started: every warp leaves
+    uint32_t abort;            // a warp waited longer than the watchdog allows: every warp leaves, the frame fails
+    uint32_t pad4[28];
+    unsigned long long stat_closest, stat_shadow, stat_samples, stat_shade_batches, stat_flex_rays, stat_idle_polls;
+};
+
 // Path / ray state, vectorised SoA in HBM, indexed by slot (one slot per owned pixel; replaces the reference's
 // SOA<PathState>, RayQueue, ShadowRayQueue, MaterialQueue: kernel/integrators/gpu/workitem.h:27-107).
 struct Workspace {
@@ -34,6 +49,11 @@ struct Workspace {
     float4 *acc;                // per-slot film accumulator (sum L | sum weight): Tile::add_sample
     uint32_t *q_ext[2], *q_sh[2], *q_shade[2][kNumKeys];
     Counters *ctr;
+    // streaming wavefront only: the two rings (1 << ring_shift entries each) and their control block
+    uint32_t *r_ring; // [31:25] tag = (ticket >> ring_shift) & 127, [24] shadow ray pending, [23] no extension ray, [22:0] slot
+    uint4 *q_ring;    // x: [31:25] tag, [24] the shadow ray was unoccluded, [23] there was a shadow ray, [22:0] slot; y: triangle (< 0: miss); z, w: u, v
+    int ring_shift;
+    StreamCtl *sc;
 };
 
 struct RenderConfig {
@@ -73,6 +93,10 @@ cudaError_t launch_wf_shade(const SceneDev &S, const RenderConfig &rc, const Wor
 // tail of a frame: one thread per entry of q_ext[parity] runs its pixel's remaining samples to completion
 cudaError_t launch_wf_finish(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int parity, uint32_t n_upper,
                              cudaStream_t st);
+// Streaming wavefront: one persistent launch renders the whole share (after launch_wf_init filled q_ext[0]).
+constexpr int kStreamMaxSlots = 1 << 23;
+cudaError_t set_stream_options(int flex_mask, int watchdog_ms);
+cudaError_t launch_wf_stream(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, int n_sms, cudaStream_t st);
 cudaError_t launch_wf_resolve(const RenderConfig &rc, const Workspace &ws, float4 *film, cudaStream_t st);
 
 // Sample-split combine over peer memory (akb_set_option("combine", "p2p")): dst[i] = ((dst[i] + film[0][i]) + film[1][i]) ...

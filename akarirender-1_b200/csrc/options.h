@@ -21,6 +21,9 @@ struct Options {
                                          // 0 never, 1 in launches with >= 4 rays per thread, 2 always
     int refill_below = 0;                // persistent traversal warps refill below this many live lanes (0: 24 / 20 by step)
     int fetch_chunk = 0;                 // >0: warp-private fetch chunks
+    int stream = 0;                      // 1: the streaming wavefront (one persistent launch per share, no barrier between bounces; kernels.cu)
+    int stream_flex_mask = 1;            // warps of a block (bit w = warp w) that prefer shading
+    int stream_watchdog_ms = 4000;       // a streaming warp idle for this long fails the frame instead of hanging the GPU
     int profile_stages = 0;              // per-stage events, one pipeline, no graphs, no finish kernel
     int timeline = 0;                    // print every poll's device time and queue lengths
     long long trace_chunk = 1ll << 21;   // rays per staging slot of akb_trace (host batches)

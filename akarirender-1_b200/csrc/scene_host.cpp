@@ -336,6 +336,9 @@ bool set_option(const char *name, const char *value, std::string *err) {
     AKB_INT_OPT(tail_share, 0, 2)
     AKB_INT_OPT(refill_below, 0, 32)
     AKB_INT_OPT(fetch_chunk, 0, 4096)
+    AKB_INT_OPT(stream, 0, 1)
+    AKB_INT_OPT(stream_flex_mask, 0, 15)
+    AKB_INT_OPT(stream_watchdog_ms, 1, 600000)
     AKB_INT_OPT(profile_stages, 0, 1)
     AKB_INT_OPT(timeline, 0, 1)
     AKB_INT_OPT(trace_chunk, 1024, 1ll << 30)
