@@ -858,6 +858,16 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
     if (streamed && opt.timeline)
         fprintf(stderr, "akb stream: gpu %d: %llu shade batches, %llu rays traced by shade-first warps, %llu idle polls\n", r->dev.index, r->h_stream->stat_shade_batches,
                 r->h_stream->stat_flex_rays, r->h_stream->stat_idle_polls);
+#ifdef AKB_STREAM_PROF
+    if (streamed)
+        for (int g = 0; g < 2; g++) {
+            const unsigned long long *pr = r->h_stream->prof + 10 * g;
+            const double all = (double)std::max<unsigned long long>(pr[0], 1);
+            fprintf(stderr, "akb stream prof (%s warps): shade %.1f%% steps %.1f%% refill %.1f%% idle %.1f%% msg %.1f%% | %llu refills, %llu steps at %.1f lanes, %llu batches (%.0f cycles each)\n",
+                    g ? "shade-first" : "tracing", 100 * pr[1] / all, 100 * pr[2] / all, 100 * pr[3] / all, 100 * pr[4] / all, 100 * pr[5] / all, pr[6], pr[7],
+                    pr[8] / (double)std::max<unsigned long long>(pr[7], 1), pr[9], pr[1] / (double)std::max<unsigned long long>(pr[9], 1));
+        }
+#endif
     if (stats) {
         memset(stats, 0, sizeof *stats);
         for (int k = 0; k < 2 && !streamed; k++) {

@@ -29,6 +29,9 @@ constexpr int kBlock = 128;
 #ifndef AKB_SHADE_MIN_BLOCKS
 #define AKB_SHADE_MIN_BLOCKS 6
 #endif
+#ifndef AKB_STREAM_MIN_BLOCKS
+#define AKB_STREAM_MIN_BLOCKS 8 // the streaming kernel holds both jobs
+#endif
 constexpr uint32_t kDeadRay = 0x80000000u; // queue-entry flag: path ends at the next shade step, nothing to trace
 constexpr uint32_t kHasShadow = 0x40000000u; // queue-entry flag: the path also has an entry in the shadow queue (wf_finish_kernel)
 constexpr uint32_t kSlotMask = ~(kDeadRay | kHasShadow);
@@ -993,7 +996,7 @@ __device__ __forceinline__ bool stream_shade_batch(const SceneDev &S, const Rend
 }
 
 template <int SAMP, bool TEX>
-__global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_stream_kernel(SceneDev S, RenderConfig rc, Workspace ws) {
+__global__ void __launch_bounds__(kBlock, AKB_STREAM_MIN_BLOCKS) wf_stream_kernel(SceneDev S, RenderConfig rc, Workspace ws) {
     const unsigned full = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31;
     StreamCtl *sc = ws.sc;
@@ -1015,6 +1018,15 @@ __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_stream_kernel
     bool starved = false;                                   // the last refill found no entry for an idle lane
     uint32_t n_closest = 0, n_shadow = 0, n_done = 0, n_batches = 0, n_flex_rays = 0, n_idle = 0;
     unsigned long long idle_since = 0;
+#ifdef AKB_STREAM_PROF
+    long long t_shade = 0, t_steps = 0, t_refill = 0, t_idle = 0, t_msg = 0, n_refill = 0, n_steps = 0, lanes_steps = 0;
+    const long long t_begin = clock64();
+#define PROF_T0() const long long prof_t0 = clock64()
+#define PROF_ADD(var) var += clock64() - prof_t0
+#else
+#define PROF_T0() ((void)0)
+#define PROF_ADD(var) ((void)0)
+#endif
 
     // Readers take tickets only for entries the ring holds (head < tail when they looked); two readers racing for the
     // same entries leave the loser with tickets whose entries come later. Such tickets are never sat on: ray-ring
@@ -1046,6 +1058,7 @@ __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_stream_kernel
         }
         const unsigned mm = __ballot_sync(full, msg);
         if (mm) {
+            PROF_T0();
             const int leader = __ffs(mm) - 1;
             uint32_t base = 0;
             if ((int)lane == leader) base = atomicAdd(&sc->q_tail, (uint32_t)__popc(mm));
@@ -1057,6 +1070,7 @@ __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_stream_kernel
                 v.y = (uint32_t)T.hit.tri, v.z = __float_as_uint(T.hit.u), v.w = __float_as_uint(T.hit.v);
                 st_relaxed4(ws.q_ring + (t & mask), v);
             }
+            PROF_ADD(t_msg);
         }
         bool progress = mm != 0;
         unsigned act = __ballot_sync(full, active);
@@ -1065,7 +1079,9 @@ __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_stream_kernel
         //      anything; the others once the ray ring has nothing for them; everybody the tickets already held ----
         if (act == 0) {
             bool did = false;
+            PROF_T0();
             if (flex || starved || q_next != q_end) did = stream_shade_batch<SAMP, TEX>(S, rc, ws, 1u, n_started, q_next, q_end, n_done);
+            PROF_ADD(t_shade);
             trav_init(T, mk3(0, 0, 0), mk3(0, 0, 1), 0.f, 0.f, false); // nothing of T lives across the shading code
             if (did) {
                 n_batches++;
@@ -1087,6 +1103,7 @@ __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_stream_kernel
             hits_waiting = (x >> 25) == ((q_next >> ws.ring_shift) & 127u);
         }
         if (idle && !hits_waiting && (!flex || act == 0)) {
+            PROF_T0();
             if (r_next == r_end) {
                 // only what the ring holds (a racing reader may still get there first: then the tickets are kept and
                 // looked at on every pass until their entries arrive)
@@ -1134,6 +1151,14 @@ __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_stream_kernel
             r_next += n_take;
             starved = n_take < (uint32_t)__popc(idle);
             if (n_take) progress = true;
+#ifdef AKB_STREAM_PROF
+            n_refill++;
+            if (cand && rank < n_take && active) { // wait for the ray: the refill's whole latency chain
+                volatile float sink = T.o.x + T.d.x;
+                (void)sink;
+            }
+#endif
+            PROF_ADD(t_refill);
         }
         act = __ballot_sync(full, active);
         const unsigned hv0 = __ballot_sync(full, have);
@@ -1153,7 +1178,11 @@ __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_stream_kernel
                 if (now - idle_since > (unsigned long long)c_stream_watchdog_ms * 1000000ull) st_relaxed(&sc->abort, 1u);
             }
             starved = true;
-            __nanosleep(400);
+            {
+                PROF_T0();
+                __nanosleep(400);
+                PROF_ADD(t_idle);
+            }
             continue;
         }
         idle_since = 0;
@@ -1161,14 +1190,29 @@ __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_stream_kernel
         //      refill (shade-first: one batch at a time; ray ring empty) sends its results a few at a time ----
         int steps = 0;
         unsigned hv = hv0;
+        PROF_T0();
         do {
+#ifdef AKB_STREAM_PROF
+            n_steps++, lanes_steps += __popc(act);
+#endif
             if (post_limit >= 0 ? trav_step_ii(T, nodes, tris, stack, active, post_limit) : (active && trav_step(T, nodes, tris, stack)))
                 active = false, have = true;
             act = __ballot_sync(full, active);
             hv = __ballot_sync(full, have);
             steps++;
         } while (act != 0 && (flex ? __popc(hv) < 8 : (__popc(act) >= refill_below || (starved && hv == 0 && steps < 8))));
+        PROF_ADD(t_steps);
     }
+#ifdef AKB_STREAM_PROF
+    if (lane == 0) {
+        const long long t_all = clock64() - t_begin;
+        unsigned long long *pr = sc->prof + (flex ? 10 : 0);
+        atomicAdd(pr + 0, (unsigned long long)t_all), atomicAdd(pr + 1, (unsigned long long)t_shade), atomicAdd(pr + 2, (unsigned long long)t_steps);
+        atomicAdd(pr + 3, (unsigned long long)t_refill), atomicAdd(pr + 4, (unsigned long long)t_idle), atomicAdd(pr + 5, (unsigned long long)t_msg);
+        atomicAdd(pr + 6, (unsigned long long)n_refill), atomicAdd(pr + 7, (unsigned long long)n_steps), atomicAdd(pr + 8, (unsigned long long)lanes_steps);
+        atomicAdd(pr + 9, (unsigned long long)n_batches);
+    }
+#endif
     // ---- statistics ----
     for (int o = 16; o > 0; o >>= 1) {
         n_closest += __shfl_down_sync(full, n_closest, o);

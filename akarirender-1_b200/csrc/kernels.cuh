@@ -31,6 +31,7 @@ struct StreamCtl {
     uint32_t abort;            // a warp waited longer than the watchdog allows: every warp leaves, the frame fails
     uint32_t pad4[28];
     unsigned long long stat_closest, stat_shadow, stat_samples, stat_shade_batches, stat_flex_rays, stat_idle_polls;
+    unsigned long long prof[20]; // -DAKB_STREAM_PROF builds: cycles per activity, [0..9] tracing warps, [10..19] shade-first warps
 };
 
 // Path / ray state, vectorised SoA in HBM, indexed by slot (one slot per owned pixel; replaces the reference's

@@ -16,6 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 rep, kregex, mangled = sys.argv[1:4]
 launch = int(sys.argv[4]) if len(sys.argv) > 4 else 0
 top = int(sys.argv[5]) if len(sys.argv) > 5 else 40
+by_samples = len(sys.argv) > 6 and sys.argv[6] == "samples"  # order by stall samples instead of issued instructions
 lib = os.environ.get("AKB_LIB", os.path.join(ROOT, "akarirender-1_b200", "libakari_b200.so"))
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "kernels", lib], cwd=tmp, check=True, capture_output=True)
@@ -63,7 +64,7 @@ def src(loc):
                 src_cache[p] = open(p).read().splitlines()
             return src_cache[p][n - 1].strip()[:90] if n - 1 < len(src_cache[p]) else ""
     return ""
-for loc, a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+for loc, a in sorted(agg.items(), key=lambda kv: -kv[1][2 if by_samples else 0])[:top]:
     if loc is None:
         continue
     print("%-14s:%4d  sass %3d  warp-instr %5.1f%%  lanes %4.1f  samples %5.1f%%  | %s" % (
