@@ -131,7 +131,7 @@ struct Flattener {
             }
         } else {
             std::vector<uint8_t> rgb;
-            read_png_rgb8(path, &w, &h, &rgb);
+            read_image_rgb8(path, &w, &h, &rgb);
             tex = std::make_unique<std::vector<float>>((size_t)w * h * 4);
             for (size_t i = 0; i < (size_t)w * h; i++) {
                 for (int k = 0; k < 3; k++) (*tex)[4 * i + k] = (float)rgb[3 * i + k] / 255.0f;

@@ -40,6 +40,12 @@ void read_mesh_file(const std::string &path, MeshData *out);
 // 8-bit PNG -> tightly packed RGB bytes, the way `stbi_load(path, &x, &y, &channel, 3)` returns them
 // (core/image.cpp:105). png_read.cpp.
 void read_png_rgb8(const std::string &path, int *width, int *height, std::vector<uint8_t> *rgb);
+// JPEG (baseline, extended sequential and progressive Huffman files) -> the same bytes, bit for bit what stb_image
+// v2.23 returns for stbi_load(..., 3). stb picks the decoder by content, so does the front-end. jpeg_read.cpp.
+bool looks_like_jpeg(const uint8_t *bytes, size_t n);
+void decode_jpeg_rgb8(const std::string &name, const uint8_t *bytes, size_t n, int *width, int *height, std::vector<uint8_t> *rgb);
+// Any 8-bit texture file the front-end reads (JPEG or PNG, by content)
+void read_image_rgb8(const std::string &path, int *width, int *height, std::vector<uint8_t> *rgb);
 // Radiance .hdr -> RGB floats, the way `stbi_loadf(path, &x, &y, &channel, 3)` returns them (core/image.cpp:85-103).
 // hdr_read.cpp.
 void read_hdr_rgb(const std::string &path, int *width, int *height, std::vector<float> *rgb);
