@@ -814,7 +814,8 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
                         poll_pending[k] = false;
                         if (opt.timeline) {
                             float ms = 0.f;
-                            cudaEventElapsedTime(&ms, r->ev0, r->ev_poll[k]);
+                            if (cudaEventElapsedTime(&ms, r->ev0, r->ev_poll[k]) != cudaSuccess) // (option set after the scene was created: no timing events)
+                                cudaGetLastError(), ms = -1.f;
                             fprintf(stderr, "akb timeline: gpu %d pipe %d after bounce %ld: %.3f ms, n_ext %u n_sh %u\n", r->dev.index, k, it - check_every,
                                     ms, r->h_ctr[k].n_ext[b ^ 1], r->h_ctr[k].n_sh[b ^ 1]);
                         }

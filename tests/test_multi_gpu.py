@@ -63,6 +63,14 @@ def test_tile_split_is_bit_identical_to_one_gpu(combine):
             p = sc.integrator.params()
             p.n_gpus, p.mode = n, abi.MODE_MEGAKERNEL
             assert same_bits(be.render(p)[0], ref)
+            # ... and so does the streaming wavefront (one persistent launch per GPU, its own rings on every replica)
+            try:
+                pkg.set_option("stream", 1)
+                p = sc.integrator.params()
+                p.n_gpus = n
+                assert same_bits(be.render(p)[0], ref)
+            finally:
+                pkg.set_option("stream", 0)
             be.close()
     finally:
         pkg.set_option("combine", "nccl")
