@@ -29,6 +29,7 @@ namespace {
 thread_local std::string g_err;
 constexpr size_t kMaxBatch = (size_t)1 << 30;
 constexpr int kMaxDevices = 16;
+constexpr int kMaxPipes = 4; // wavefront pipelines per GPU (option pipelines)
 
 // A CUDA device this process was bound to by akb_init / akb_init_device.
 struct Device {
@@ -143,10 +144,10 @@ struct Replica {
     Workspace ws;
     std::vector<void *> ws_allocs;
     int ws_slots = 0;
-    Counters *d_ctr = nullptr, *h_ctr = nullptr; // [2]: one per half-frame pipeline
+    Counters *d_ctr = nullptr, *h_ctr = nullptr; // [kMaxPipes]: one per pipeline
     cudaStream_t main_stream = nullptr;          // multi-GPU frames and host-buffer entry points run here
-    cudaStream_t aux_stream = nullptr;           // second pipeline's stream
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_poll[2] = {nullptr, nullptr};
+    cudaStream_t aux_stream[kMaxPipes - 1] = {}; // the further pipelines' streams
+    cudaEvent_t ev_fork = nullptr, ev_join[kMaxPipes - 1] = {}, ev_poll[kMaxPipes] = {};
     float4 *d_film = nullptr;
     size_t d_film_px = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -167,7 +168,7 @@ struct Replica {
         RenderConfig rc;
         Workspace ws;
         int n_bounces = 0;
-    } bounce_graph[2];
+    } bounce_graph[kMaxPipes];
     cudaStream_t cap_stream = nullptr;
     // streaming wavefront (option stream): the two rings and their control block, sized with the workspace
     uint32_t *r_ring = nullptr;
@@ -224,9 +225,11 @@ struct Replica {
         if (h_film) cudaFreeHost(h_film);
         for (cudaEvent_t e : ev_chunk) cudaEventDestroy(e);
         if (main_stream) cudaStreamDestroy(main_stream);
-        if (aux_stream) cudaStreamDestroy(aux_stream);
+        for (cudaStream_t a : aux_stream)
+            if (a) cudaStreamDestroy(a);
         if (ev_fork) cudaEventDestroy(ev_fork);
-        if (ev_join) cudaEventDestroy(ev_join);
+        for (cudaEvent_t e : ev_join)
+            if (e) cudaEventDestroy(e);
         for (cudaEvent_t e : ev_poll)
             if (e) cudaEventDestroy(e);
         if (ev0) cudaEventDestroy(ev0);
@@ -530,15 +533,16 @@ akb_status make_replica(const HostScene &hs, const Device &dev, Replica *r) {
     }
     if (st != AKB_OK) return st;
     const bool timeline = options().timeline != 0;
-    CU(cudaMalloc((void **)&r->d_ctr, 2 * sizeof(Counters)));
-    CU(cudaMallocHost((void **)&r->h_ctr, 2 * sizeof(Counters)));
+    CU(cudaMalloc((void **)&r->d_ctr, kMaxPipes * sizeof(Counters)));
+    CU(cudaMallocHost((void **)&r->h_ctr, kMaxPipes * sizeof(Counters)));
     CU(cudaStreamCreateWithFlags(&r->main_stream, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&r->aux_stream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&r->ev_fork, cudaEventDisableTiming));
-    CU(cudaEventCreateWithFlags(&r->ev_join, cudaEventDisableTiming));
+    for (int k = 0; k + 1 < kMaxPipes; k++) {
+        CU(cudaStreamCreateWithFlags(&r->aux_stream[k], cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&r->ev_join[k], cudaEventDisableTiming));
+    }
     CU(cudaStreamCreateWithFlags(&r->cap_stream, cudaStreamNonBlocking));
-    CU(cudaEventCreateWithFlags(&r->ev_poll[0], timeline ? cudaEventDefault : cudaEventDisableTiming));
-    CU(cudaEventCreateWithFlags(&r->ev_poll[1], timeline ? cudaEventDefault : cudaEventDisableTiming));
+    for (int k = 0; k < kMaxPipes; k++) CU(cudaEventCreateWithFlags(&r->ev_poll[k], timeline ? cudaEventDefault : cudaEventDisableTiming));
     CU(cudaEventCreate(&r->ev0));
     CU(cudaEventCreate(&r->ev1));
     S.light_func_int = hs.light_func_int;
@@ -691,7 +695,7 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
     std::vector<cudaEvent_t> evs;
     const bool profile_stages = opt.profile_stages != 0;
     if (!film_is_shared) CU(cudaMemsetAsync(film, 0, n_px * sizeof(float4), stream));
-    CU(cudaMemsetAsync(r->d_ctr, 0, 2 * sizeof(Counters), stream));
+    CU(cudaMemsetAsync(r->d_ctr, 0, kMaxPipes * sizeof(Counters), stream));
     CU(cudaEventRecord(r->ev0, stream));
     if (p->integrator == AKB_INTEGRATOR_AO && p->mode == AKB_MODE_MEGAKERNEL) {
         CU(launch_ao(r->S, rc, p->ao_occlude, film, r->d_ctr, stream));
@@ -720,22 +724,32 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
         const int n_total = rc.map.n_slots();
         akb_status st = ensure_workspace(r, n_total);
         if (st != AKB_OK) return st;
-        // Two half-frame pipelines on two streams: while one half's traversal launch drains (persistent warps running
-        // their last, longest rays at a few lanes each) the other half's kernels fill the machine. Halves are whole
-        // tiles, so every slot keeps its pixel, seed and accumulation order: the film is unchanged.
+        // Up to four pipelines on as many streams (default two), each a contiguous range of the owned tiles with its own
+        // queues and counters: while one pipeline's traversal launch drains (persistent warps running their last,
+        // longest rays at a few lanes each) the others' kernels fill the machine. Every slot keeps its pixel's seed and
+        // accumulation order: the film is unchanged. Measured on C3 (profiles/r02_notes.md section 10): 1 / 2 / 3 / 4
+        // pipelines 113.6 / 111.2 / 114.2 / 109.9 ms; dealing the tiles out in turn (option pipeline_interleave), so that
+        // all pipelines hold the same mix of sky and ground pixels, makes two pipelines as slow as one (113.5 ms): the
+        // pipelines then move in step, and what two pipelines win comes from their being out of step.
         const int tt = rc.map.tile * rc.map.tile;
-        const int n_pipes = (opt.pipelines >= 2 && !profile_stages && rc.map.n_owned_tiles >= 2 && n_total >= opt.pipeline_min_slots) ? 2 : 1;
-        const int base1 = n_pipes == 2 ? (rc.map.n_owned_tiles / 2) * tt : n_total;
+        int n_pipes = (!profile_stages && n_total >= opt.pipeline_min_slots) ? std::min(opt.pipelines, rc.map.n_owned_tiles) : 1;
+        n_pipes = std::max(1, std::min(n_pipes, kMaxPipes));
+        rc.map.groups = opt.pipeline_interleave ? n_pipes : 1;
         struct Pipe {
             Workspace ws;
             cudaStream_t st;
             bool live;
-        } pipe[2];
-        pipe[0] = Pipe{workspace_view(r->ws, 0, base1, r->d_ctr), stream, n_total > 0 && rc.spp > 0};
-        pipe[1] = Pipe{workspace_view(r->ws, base1, n_total - base1, r->d_ctr + 1), r->aux_stream, n_pipes == 2 && rc.spp > 0};
-        if (n_pipes == 2) {
+        } pipe[kMaxPipes];
+        for (int k = 0, base = 0; k < n_pipes; k++) {
+            // (contiguous ranges: the same sizes, so that both settings cut the workspace alike)
+            const int n_k = ((rc.map.n_owned_tiles - k + n_pipes - 1) / n_pipes) * tt;
+            pipe[k] = Pipe{workspace_view(r->ws, base, n_k, r->d_ctr + k), k == 0 ? stream : r->aux_stream[k - 1], n_k > 0 && rc.spp > 0};
+            base += n_k;
+        }
+        for (int k = n_pipes; k < kMaxPipes; k++) pipe[k].live = false;
+        if (n_pipes > 1) {
             CU(cudaEventRecord(r->ev_fork, stream));
-            CU(cudaStreamWaitEvent(r->aux_stream, r->ev_fork, 0));
+            for (int k = 1; k < n_pipes; k++) CU(cudaStreamWaitEvent(pipe[k].st, r->ev_fork, 0));
         }
         for (int k = 0; k < n_pipes; k++) {
             CU(launch_wf_init(r->S, rc, pipe[k].ws, n_sms, pipe[k].st));
@@ -743,7 +757,7 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
         }
         const long max_it = (long)rc.spp * (rc.max_depth + 2) + 2;
         const int check_every = opt.check_every; // even: a snapshot taken after an odd bounce is read after an odd bounce
-        bool poll_pending[2] = {false, false};
+        bool poll_pending[kMaxPipes] = {};
         auto mark = [&]() {
             if (!profile_stages) return cudaSuccess;
             cudaEvent_t e;
@@ -775,7 +789,12 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
                 CU(ce);
                 g.rc = rc, g.ws = pipe[k].ws, g.n_bounces = check_every;
             }
-        for (long it = 0; it < max_it && (pipe[0].live || pipe[1].live); it++) {
+        auto any_live = [&]() {
+            for (int k = 0; k < n_pipes; k++)
+                if (pipe[k].live) return true;
+            return false;
+        };
+        for (long it = 0; it < max_it && any_live(); it++) {
             const int b = (int)(it & 1);
             if (use_graphs) {
                 if ((it % check_every) == 0)
@@ -838,9 +857,9 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
                 }
             }
         }
-        if (n_pipes == 2) {
-            CU(cudaEventRecord(r->ev_join, r->aux_stream));
-            CU(cudaStreamWaitEvent(stream, r->ev_join, 0));
+        for (int k = 1; k < n_pipes; k++) {
+            CU(cudaEventRecord(r->ev_join[k - 1], pipe[k].st));
+            CU(cudaStreamWaitEvent(stream, r->ev_join[k - 1], 0));
         }
         for (int k = 0; k < n_pipes; k++) {
             // "Film accumulate": slot accumulators -> the film; with a shared film this store goes over NVLink into
@@ -850,7 +869,7 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
         }
     }
     CU(cudaEventRecord(r->ev1, stream));
-    CU(cudaMemcpyAsync(r->h_ctr, r->d_ctr, 2 * sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+    CU(cudaMemcpyAsync(r->h_ctr, r->d_ctr, kMaxPipes * sizeof(Counters), cudaMemcpyDeviceToHost, stream));
     if (streamed) CU(cudaMemcpyAsync(r->h_stream, r->d_stream, sizeof(StreamCtl), cudaMemcpyDeviceToHost, stream));
     CU(cudaStreamSynchronize(stream));
     if (streamed && (r->h_stream->abort || !r->h_stream->done))
@@ -871,7 +890,7 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
 #endif
     if (stats) {
         memset(stats, 0, sizeof *stats);
-        for (int k = 0; k < 2 && !streamed; k++) {
+        for (int k = 0; k < kMaxPipes && !streamed; k++) {
             stats->n_samples += r->h_ctr[k].stat_samples;
             stats->n_closest_rays += r->h_ctr[k].stat_closest - r->h_ctr[k].stat_skipped;
             stats->n_shadow_rays += r->h_ctr[k].stat_shadow;

@@ -8,7 +8,9 @@ namespace akb {
 
 struct Options {
     // wavefront scheduling (api.cu)
-    int pipelines = 2;                   // half-frame pipelines of the wavefront (1 or 2)
+    int pipelines = 2;                   // pipelines of the wavefront: the owned tiles in 1..4 groups, each with its own queues and stream
+    int pipeline_interleave = 0;         // 1: tiles are dealt out to the pipelines in turn (all see the same mix of sky and ground; measured
+                                         // slower: pipelines then move in step and might as well be one); 0: contiguous ranges of tiles
     int pipeline_min_slots = 128 * 1024; // below this many paths one pipeline keeps the launches large
     int graphs = 1;                      // 0: launch every bounce's kernels one by one
     int check_every = 4;                 // bounces per graph launch / queue-length poll (even)

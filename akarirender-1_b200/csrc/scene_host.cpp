@@ -325,7 +325,8 @@ bool set_option(const char *name, const char *value, std::string *err) {
         o.field = (decltype(o.field))i;                                                                                \
         return true;                                                                                                   \
     }
-    AKB_INT_OPT(pipelines, 1, 2)
+    AKB_INT_OPT(pipelines, 1, 4)
+    AKB_INT_OPT(pipeline_interleave, 0, 1)
     AKB_INT_OPT(pipeline_min_slots, 0, 1 << 30)
     AKB_INT_OPT(graphs, 0, 1)
     AKB_INT_OPT(poll_lag, 0, 1)
@@ -381,7 +382,7 @@ SlotMap make_slot_map(int width, int height, int tile, int rank, int world) {
     SlotMap m;
     m.width = width, m.height = height, m.tile = tile;
     m.tiles_x = (width + tile - 1) / tile, m.tiles_y = (height + tile - 1) / tile;
-    m.rank = rank, m.world = world;
+    m.rank = rank, m.world = world, m.groups = 1;
     int nt = m.tiles_x * m.tiles_y;
     m.n_owned_tiles = nt > rank ? (nt - rank + world - 1) / world : 0;
     return m;

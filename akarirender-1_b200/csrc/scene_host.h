@@ -65,7 +65,12 @@ akb_status flatten_scene(const akb_scene_desc *desc, int n_threads, HostScene *o
 struct SlotMap {
     int width, height, tile, tiles_x, tiles_y, rank, world;
     int n_owned_tiles;
+    // The wavefront's pipelines (api.cu) are contiguous slot ranges; `groups` > 1 deals the owned tiles out to them in
+    // turn (tile i of this rank -> group i % groups), so that every pipeline sees the whole picture - sky and ground
+    // alike - and they run out of paths together. Slot order only: which pixel a slot is changes, never a pixel's result.
+    int groups;
     AKB_HD int n_slots() const { return n_owned_tiles * tile * tile; }
+    AKB_HD int group_tiles(int g) const { return (n_owned_tiles - g + groups - 1) / groups; } // owned tiles i with i % groups == g
 };
 SlotMap make_slot_map(int width, int height, int tile, int rank, int world);
 
@@ -89,7 +94,13 @@ AKB_HD uint32_t morton_compact(uint32_t v) { // even bits of v -> low half
 // false when the slot falls outside the image (edge tiles)
 AKB_HD bool slot_to_pixel(const SlotMap &m, int slot, int &x, int &y) {
     const int tt = m.tile * m.tile;
-    const int lt = slot / tt, in = slot - lt * tt;
+    int lt = slot / tt;
+    const int in = slot - lt * tt;
+    if (m.groups > 1) { // position in slot order -> (group, index in group) -> owned tile
+        int g = 0;
+        for (int c = m.group_tiles(0); g + 1 < m.groups && lt >= c; c = m.group_tiles(g)) lt -= c, g++;
+        lt = lt * m.groups + g;
+    }
     const int t = lt * m.world + m.rank;
     const int ty = t / m.tiles_x, tx = t - ty * m.tiles_x;
     x = tx * m.tile + (int)morton_compact((uint32_t)in);
