@@ -916,11 +916,27 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
     return AKB_OK;
 }
 
+// Page-locked host memory (cudaHostAlloc / cudaHostRegister by the caller): the DMA engines reach it directly, so the
+// host-buffer entry points copy straight from / into it instead of through the library's own pinned staging.
+bool host_pinned(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
 // Device film -> caller's host buffer through a pinned staging buffer: the copy is cut into chunks, and while chunk k
 // crosses PCIe a few host threads move the chunks already landed into the caller's (pageable) memory.
 akb_status download_film(Replica *r, float *out, size_t n_px, cudaStream_t stream) {
     const size_t bytes = n_px * sizeof(float4);
     if (bytes == 0) return AKB_OK;
+    if (host_pinned(out)) { // the caller's buffer is page-locked: one DMA, no staging
+        CU(cudaMemcpyAsync(out, r->d_film, bytes, cudaMemcpyDeviceToHost, stream));
+        CU(cudaStreamSynchronize(stream));
+        return AKB_OK;
+    }
     if (r->h_film_bytes < bytes) {
         if (r->h_film) cudaFreeHost(r->h_film);
         r->h_film = nullptr, r->h_film_bytes = 0;
@@ -1162,6 +1178,25 @@ akb_status akb_trace(akb_scene *sc, const float *org, const float *dir, size_t n
     }
     char *out = any_hit ? (char *)out_occ : (char *)out_hits;
     const size_t n_chunks = (n + chunk - 1) / chunk;
+    if (e == cudaSuccess && host_pinned(org) && host_pinned(dir) && host_pinned(out)) {
+        // Page-locked caller buffers: every chunk is H2D, kernel, D2H on its slot's stream, straight from / into the
+        // caller's memory; the two slots' streams overlap both PCIe directions with the traversal, and stream order is
+        // all the synchronisation there is until the end.
+        for (size_t k = 0; k < n_chunks && e == cudaSuccess; k++) {
+            Replica::TraceSlot &t = r->trace_slot[k & 1];
+            const size_t off = k * chunk, m = std::min(chunk, n - off);
+            e = cudaMemcpyAsync(t.d_o, org + 4 * off, m * sizeof(float4), cudaMemcpyHostToDevice, t.st);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(t.d_d, dir + 4 * off, m * sizeof(float4), cudaMemcpyHostToDevice, t.st);
+            if (e == cudaSuccess) e = launch_trace_batch(r->S, t.d_o, t.d_d, m, any_hit, (akb_hit *)t.d_out, (int32_t *)t.d_out, t.cursor, r->dev.n_sms, t.st);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(out + off * out_elt, t.d_out, m * out_elt, cudaMemcpyDeviceToHost, t.st);
+        }
+        for (Replica::TraceSlot &t : r->trace_slot) {
+            const cudaError_t rr = cudaStreamSynchronize(t.st);
+            if (e == cudaSuccess) e = rr;
+        }
+        if (e != cudaSuccess) return set_err(AKB_CUDA_ERROR, "akb_trace: %s", cudaGetErrorString(e));
+        return AKB_OK;
+    }
     auto drain = [&](size_t k) { // chunk k's results: wait for its slot, then pinned -> caller
         Replica::TraceSlot &t = r->trace_slot[k & 1];
         cudaError_t rr = cudaStreamSynchronize(t.st);

@@ -543,107 +543,6 @@ __global__ void __launch_bounds__(kBlock, AKB_TRACE_MIN_BLOCKS) wf_trace_kernel(
     }
 }
 
-// Path state in HBM is read through L1 by the bounce-synchronous kernels (a kernel boundary separates writer and reader)
-// and past it (ld.global.cg: L2 is the point of coherence) by the streaming kernel, whose writers and readers run at
-// the same time on different SMs.
-template <bool STREAM, class V> __device__ __forceinline__ V ldw(const V *p) {
-    if (STREAM) return __ldcg(p);
-    return *p;
-}
-
-// One shade step of one path, shared by wf_shade_kernel and the streaming kernel: the closest-hit result (hu, hv, tri;
-// tri < 0 = miss or a parked entry) of the path in `slot` -> path_vertex, the next extension ray and the shadow ray
-// written to the slot, finished samples added to the slot accumulator and the pixel's next sample started in place.
-// Out: push_ext / ext_entry (the slot goes on: traced, or parked with kDeadRay), push_sh (a shadow ray was written),
-// slot_done (the pixel's last sample is in the accumulator: nothing more to do for this slot).
-template <int SAMP, bool TEX, bool AO, bool STREAM>
-__device__ __forceinline__ bool shade_vertex(const SceneDev &S, const RenderConfig &rc, const Workspace &ws, uint32_t slot, float hu, float hv,
-                                             int tri, bool &push_ext, bool &push_sh, uint32_t &ext_entry, uint32_t &n_done,
-                                             uint32_t &n_parked) {
-    bool slot_done = false;
-    ext_entry = slot;
-    PathState<SAMP> ps;
-    ps.rng.s = ldw<STREAM>(ws.rng + slot);
-    ps.L = mk3(0, 0, 0); // running L stays in HBM; path_vertex only ever adds emission, at depth 0
-    bool finished = true; // path ends at this vertex
-    if (AO) {
-        if (tri >= 0) {
-            const RaySeg sh = ao_ray<SAMP>(S, ps.rng, hu, hv, tri, rc.ao_occlude);
-            ws.sh_o[slot] = mk4(sh.o, sh.tmin);
-            ws.sh_d[slot] = mk4(sh.d, sh.tmax);
-            ws.sh_c[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-            ws.rng[slot] = ps.rng.s;
-            ext_entry = slot | kDeadRay;
-            push_sh = push_ext = true, finished = false;
-            n_parked++;
-        }
-    } else if (tri >= 0) {
-        const float4 bd = ldw<STREAM>(ws.beta + slot);
-        const float4 rd = ldw<STREAM>(ws.ray_d + slot);
-        ps.beta = xyz(bd), ps.depth = __float_as_int(bd.w);
-        RaySeg next, sh;
-        v3 sc;
-        const int fl = path_vertex<SAMP>(S, ps, xyz(rd), hu, hv, tri, rc.max_depth, rc.rr_start, next, sh, sc, TEX);
-        bool cont = (fl & VTX_CONTINUE) != 0;
-        const bool shadow = (fl & VTX_SHADOW) != 0;
-        // A ray leaving a vertex at depth == max_depth can never contribute (kernel/pathtracer.h:102-112: no
-        // emission at depth > 0, no scattering at depth >= max_depth): it is not traced.
-        if (cont && ps.depth >= rc.max_depth && ps.depth > 0) cont = false;
-        if (shadow) {
-            ws.sh_o[slot] = mk4(sh.o, sh.tmin);
-            ws.sh_d[slot] = mk4(sh.d, sh.tmax);
-            ws.sh_c[slot] = mk4(sc, 0.f);
-            push_sh = true;
-        }
-        if (cont) {
-            ws.ray_o[slot] = mk4(next.o, next.tmin);
-            ws.ray_d[slot] = mk4(next.d, next.tmax);
-            ws.beta[slot] = mk4(ps.beta, __int_as_float(ps.depth));
-            ws.rng[slot] = ps.rng.s;
-            push_ext = true, finished = false;
-        } else if (shadow) {
-            // The path ends here, but the film add must wait for this vertex's shadow ray.
-            const float4 Lr = ldw<STREAM>(ws.L + slot);
-            const int done = __float_as_int(Lr.w) + 1;
-            if (done < rc.spp && g_no_park) {
-                // The pixel starts its next sample now; the traversal step that resolves the shadow ray adds
-                // the finished sample to the film (both possible values are worked out here).
-                ws.sh_c[slot] = mk4(clamp_sample(add3(xyz(Lr), sc), rc.ray_clamp), 1.f);
-                ws.sh_b[slot] = mk4(clamp_sample(xyz(Lr), rc.ray_clamp), 0.f);
-                n_done++;
-                int x, y;
-                slot_to_pixel(rc.map, (int)slot + ws.slot_base, x, y);
-                start_sample<SAMP>(S, ws, (int)slot, x, y, ps.rng, done);
-                push_ext = true, finished = false;
-            } else {
-                // last sample of the pixel: park the path for one step
-                ws.rng[slot] = ps.rng.s;
-                ext_entry = slot | kDeadRay;
-                push_ext = true, finished = false;
-                n_parked++; // the queue entry is counted by the next traversal launch but traces nothing
-            }
-        }
-    }
-    if (finished) { // "Splat" + regenerate (gpu/cuda/integrator.cpp:385-401, core/film.h:66-70)
-        const float4 Lr = ldw<STREAM>(ws.L + slot);
-        const v3 L = add3(xyz(Lr), ps.L); // ps.L != 0 only for a camera-visible emitter, where Lr.xyz == 0
-        const int done = __float_as_int(Lr.w) + 1;
-        float4 a = ldw<STREAM>(ws.acc + slot);
-        const v3 s = add3(xyz(a), clamp_sample(L, rc.ray_clamp));
-        ws.acc[slot] = make_float4(s.x, s.y, s.z, a.w + 1.0f);
-        n_done++;
-        if (done < rc.spp) {
-            int x, y;
-            slot_to_pixel(rc.map, (int)slot + ws.slot_base, x, y);
-            start_sample<SAMP>(S, ws, (int)slot, x, y, ps.rng, done);
-            push_ext = true;
-        } else {
-            slot_done = true;
-        }
-    }
-    return slot_done;
-}
-
 // AO = true: the AO integrator on the same queues (kernel/integrators/cpu/integrator.cpp:72-80): a hit vertex emits one
 // cosine-weighted any-hit ray carrying (1,1,1) and the path parks for one step, so that the sample is 1 iff that ray
 // is unoccluded; a miss finishes with 0. Sampler order and film sums are those of ao_kernel.
@@ -713,9 +612,15 @@ __global__ void __launch_bounds__(kBlock, AKB_SHADE_MIN_BLOCKS) wf_shade_kernel(
             if (valid) slot = s_slot[threadIdx.x], hrec = s_hit[threadIdx.x];
             __syncthreads(); // the arrays are rewritten by the next round
         }
-        if (valid)
-            shade_vertex<SAMP, TEX, AO, false>(S, rc, ws, slot, hrec.x, hrec.y, __float_as_int(hrec.z), push_ext, push_sh, ext_entry, n_done,
-                                               n_parked);
+        if (valid) {
+            const float hit_u = hrec.x, hit_v = hrec.y;
+            const int tri = __float_as_int(hrec.z);
+            bool slot_done = false; // (only the streaming kernel counts finished slots)
+#define AKB_WS_LD(p) (*(p))
+#include "shade_vertex.inc"
+#undef AKB_WS_LD
+            (void)slot_done;
+        }
         if (push_sh) ext_entry |= kHasShadow; // a shadow ray always comes with an extension entry (continuing or parked)
         AKB_CHECK(!valid || slot < (uint32_t)ws.n_slots);
         queue_push2(push_ext, ext_entry, ws.q_ext[b ^ 1], &ctr->n_ext[b ^ 1], push_sh, slot, ws.q_sh[b ^ 1], &ctr->n_sh[b ^ 1], (uint32_t)ws.n_slots);
@@ -852,6 +757,7 @@ __global__ void __launch_bounds__(256) film_sum_peers_kernel(float4 *__restrict_
     }
 }
 
+#ifndef AKB_NO_STREAM // (development switch: a build without the streaming kernel, for A/B runs)
 // ---------------------------------------------------------------------------------------------------------------------
 // Streaming wavefront (akb_set_option("stream", 1)): ONE persistent launch renders the whole share, with no barrier
 // between bounces. The bounce-synchronous kernels above pay, on every one of a frame's spp x depth rounds, for the
@@ -972,8 +878,12 @@ __device__ __forceinline__ bool stream_shade_batch(const SceneDev &S, const Rend
                 ws.L[slot] = L;
             }
         }
-        slot_done = shade_vertex<SAMP, TEX, false, true>(S, rc, ws, slot, __uint_as_float(e.z), __uint_as_float(e.w), (int)e.y, push_ext, push_sh,
-                                                         ext_entry, n_done, n_parked);
+        const float hit_u = __uint_as_float(e.z), hit_v = __uint_as_float(e.w);
+        const int tri = (int)e.y;
+        constexpr bool AO = false;
+#define AKB_WS_LD(p) __ldcg(p)
+#include "shade_vertex.inc"
+#undef AKB_WS_LD
     }
     fence_release(); // the rays and the path state written above reach L2 before the ring entries that announce them
     const unsigned pm = __ballot_sync(full, push_ext);
@@ -1230,6 +1140,8 @@ __global__ void __launch_bounds__(kBlock, AKB_STREAM_MIN_BLOCKS) wf_stream_kerne
     }
 }
 
+#endif // AKB_NO_STREAM
+
 template <class K> int blocks_per_sm(K kernel, int block) {
     int n = 1;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, block, 0) != cudaSuccess || n < 1) n = 1;
@@ -1374,6 +1286,10 @@ cudaError_t launch_film_sum_peers(float4 *dst, const PeerFilms &peers, size_t n_
     return cudaGetLastError();
 }
 
+#ifdef AKB_NO_STREAM
+cudaError_t set_stream_options(int, int) { return cudaSuccess; }
+cudaError_t launch_wf_stream(const SceneDev &, const RenderConfig &, const Workspace &, int, cudaStream_t) { return cudaErrorNotSupported; }
+#else
 cudaError_t set_stream_options(int flex_mask, int watchdog_ms) {
     cudaError_t e = cudaMemcpyToSymbol(c_stream_flex_mask, &flex_mask, sizeof(int));
     if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_stream_watchdog_ms, &watchdog_ms, sizeof(int));
@@ -1398,6 +1314,7 @@ cudaError_t launch_wf_stream(const SceneDev &S, const RenderConfig &rc, const Wo
         wf_stream_kernel<AKB_SAMPLER_LCG, false><<<grid, kBlock, 0, st>>>(S, rc, ws);
     return cudaGetLastError();
 }
+#endif // AKB_NO_STREAM
 
 cudaError_t launch_wf_resolve(const RenderConfig &rc, const Workspace &ws, float4 *film, cudaStream_t st) {
     if (ws.n_slots == 0) return cudaSuccess;

@@ -222,7 +222,8 @@ def path_workload_one_gpu(pkg, torch, workload, spp, steps, warmup, bvh, mode, l
     samples, n_c, n_s, launches = acc
     # ---- end to end through the host-buffer C-ABI call a reference maintainer would bind (akb_render): every step
     # passes the parameters from host memory and reads the film back to a host buffer inside the timed region.
-    host_film = np.zeros((H, W, 4), np.float32)
+    host_film_t = torch.zeros((H, W, 4), dtype=torch.float32, pin_memory=True)  # page-locked: the library copies straight into it
+    host_film = host_film_t.numpy()
     be.render(p, out=host_film)
     e2e_steps = max(1, min(steps, 3))
     t = time.perf_counter()
@@ -276,7 +277,7 @@ def path_workload_one_gpu(pkg, torch, workload, spp, steps, warmup, bvh, mode, l
                       "bvh_nodes": info["n_bvh_nodes"], "scene_build_s": round(build_s, 2),
                       "bvh_build": {1: "host SAH", 2: "device PLOC"}.get(info["bvh_build"]), "bvh_build_s": round(info["build_us"] / 1e6, 3)},
            "e2e": {"value": e2e_samples / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": C.sizeof(pkg.abi.RenderParams),
-                   "d2h_bytes_per_step": W * H * 16, "api": "akb_render (host film buffer)"},
+                   "d2h_bytes_per_step": W * H * 16, "api": "akb_render (page-locked host film buffer)"},
            "gpu_launches": int(launches),
            "rays": {"closest_per_sample": n_c / samples, "shadow_per_sample": n_s / samples,
                     "mrays_per_s": (n_c + n_s) / (ms_total * 1e-3) / 1e6},
@@ -707,8 +708,11 @@ def bench_c2(pkg, a, local, torch, steps, warmup, headline):
     # ---- end to end: akb_trace with HOST ray and hit buffers (H2D + kernel + D2H inside the timed region), the FULL
     # incoherent set
     m = n
-    ho, hd = org2.cpu().numpy(), dr2.cpu().numpy()
-    hh = np.zeros(m, pkg.HIT_DTYPE)
+    # page-locked host buffers (the contract's "inputs in pinned host memory"): akb_trace then copies straight from / into
+    # them, chunk by chunk on two streams; pageable buffers would go through the library's own pinned staging slots
+    ho_t, hd_t = org2.cpu().pin_memory(), dr2.cpu().pin_memory()
+    hh_t = torch.zeros(m * 5, dtype=torch.int32, pin_memory=True)
+    ho, hd, hh = ho_t.numpy(), hd_t.numpy(), hh_t.numpy().view(pkg.HIT_DTYPE)
     be.trace(ho[:1 << 22], hd[:1 << 22], out=hh[:1 << 22])  # warm-up: the library sizes and pins its staging slots on the first call
     e2e_s = float("inf")
     for _ in range(2):
@@ -741,7 +745,7 @@ def bench_c2(pkg, a, local, torch, steps, warmup, headline):
                        "primary_hit_fraction": hit_frac},
             "clocks": clk,
             "e2e": {"value": m / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": m * 32, "d2h_bytes_per_step": m * 20,
-                    "api": "akb_trace (host ray + hit buffers), all %d incoherent closest-hit rays" % m},
+                    "api": "akb_trace (page-locked host ray + hit buffers), all %d incoherent closest-hit rays" % m},
             "gpu_launches": 4 * steps, "mrays_per_s": mrays,
             "roofline": {"bound": "hbm", "kernel": "trace_batch_kernel (closest hit)", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,

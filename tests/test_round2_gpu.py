@@ -138,3 +138,35 @@ def test_srgb8_bytes_bit_exact(G2):
         assert np.array_equal(be.film_to_srgb8(G[key]), G2["srgb8_" + key]), key
     assert np.array_equal(be.film_to_srgb8(G2["srgb8_ramp_in"]), G2["srgb8_ramp"])
     be.close()
+
+
+def test_page_locked_host_buffers_take_the_direct_path():
+    """akb_trace / akb_render given page-locked host buffers copy straight from / into them (two streams, no staging);
+    pageable buffers go through the library's pinned staging slots. Same bytes either way, ragged chunk counts included."""
+    import torch
+    sc = scenes.terrain_scene(n=96, resolution=(96, 54), spp=3, max_depth=6, materials="c3")
+    be = pkg.Backend(sc, 0)
+    rng = np.random.default_rng(3)
+    n = 300_001
+    o = rng.uniform((-40, 2, -40), (40, 30, 40), (n, 3)).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    org = np.concatenate([o, np.full((n, 1), 1e-3, np.float32)], 1)
+    dr = np.concatenate([d, np.full((n, 1), 60.0, np.float32)], 1)
+    want, want_occ = be.trace(org, dr), be.trace(org, dr, any_hit=True)
+    try:
+        pkg.set_option("trace_chunk", 65536)  # five chunks, the last one ragged
+        org_p, dr_p = torch.from_numpy(org).pin_memory(), torch.from_numpy(dr).pin_memory()
+        hits_p = torch.zeros(n * 5, dtype=torch.int32, pin_memory=True)
+        occ_p = torch.zeros(n, dtype=torch.int32, pin_memory=True)
+        got = be.trace(org_p.numpy(), dr_p.numpy(), out=hits_p.numpy().view(pkg.HIT_DTYPE))
+        assert got.tobytes() == want.tobytes()
+        assert np.array_equal(be.trace(org_p.numpy(), dr_p.numpy(), any_hit=True, out=occ_p.numpy()), want_occ)
+        assert got.tobytes() == be.trace(org, dr).tobytes()  # pageable, chunked through the staging slots
+    finally:
+        pkg.set_option("trace_chunk", 1 << 21)
+    film, _ = be.render()
+    film_p = torch.zeros((54, 96, 4), dtype=torch.float32, pin_memory=True)
+    be.render(out=film_p.numpy())
+    assert same_bits(film_p.numpy(), film)
+    be.close()
