@@ -22,9 +22,12 @@
 namespace akb {
 namespace {
 
-constexpr int kBlock = 128;
+#ifndef AKB_BLOCK
+#define AKB_BLOCK 128 // threads per block of the traversal / shade kernels (the *_MIN_BLOCKS below count blocks of this size)
+#endif
+constexpr int kBlock = AKB_BLOCK;
 #ifndef AKB_TRACE_MIN_BLOCKS
-#define AKB_TRACE_MIN_BLOCKS 8 // traversal kernels: 64 registers, no spills; measured 4 / 6 / 8 / 10 blocks: 29.3 / 23.6 / 22.2 / 24.7 ms
+#define AKB_TRACE_MIN_BLOCKS 8 // traversal kernels: 64 registers, no spills; measured 4 / 6 / 7 / 8 / 9 / 10 blocks: 29.3 / 23.6 / 22.7 / 21.9 - 22.2 / 22.8 / 24.7 ms
 #endif
 #ifndef AKB_SHADE_MIN_BLOCKS
 #define AKB_SHADE_MIN_BLOCKS 7 // shade kernel: 72 registers; measured 4 / 5 / 6 / 7 / 8 blocks: C3 shade stage 8.58 / 7.69 / 7.32 / 7.15 / 7.90 ms, frame 28.83 / 28.18 / 28.12 / 27.59 / 28.13 ms
