@@ -447,6 +447,19 @@ template <int SAMP> __global__ void __launch_bounds__(256) wf_init_kernel(SceneD
 
 // One launch per bounce: items [0, n_ext) are extension rays (closest hit), [n_ext, n_ext + n_sh) the shadow rays the
 // previous shade step emitted (any hit; unoccluded ones add their carried radiance to the path's L).
+// Path state read by the traversal step is read once per launch: how those loads treat L1 (which the BVH nodes live in)
+// is a build switch for A/B runs: 0 plain loads, 1 ld.global.cs (streaming), 2 ld.global.cg (past L1). Measured on C3
+// (16 spp): 27.62 - 27.64 / 27.76 - 27.89 / 27.71 - 27.73 ms - nothing to win: the default stays plain loads.
+#ifndef AKB_WF_STREAM_LOADS
+#define AKB_WF_STREAM_LOADS 0
+#endif
+#if AKB_WF_STREAM_LOADS == 1
+#define AKB_WF_LD(p) __ldcs(p)
+#elif AKB_WF_STREAM_LOADS == 2
+#define AKB_WF_LD(p) __ldcg(p)
+#else
+#define AKB_WF_LD(p) (*(p))
+#endif
 template <int SAMP> struct WfSrc {
     const SceneDev &S;
     const RenderConfig &rc;
@@ -455,19 +468,19 @@ template <int SAMP> struct WfSrc {
     uint32_t n_ext;
     __device__ __forceinline__ bool load(uint32_t i, Trav &T, uint32_t &slot) const {
         if (i < n_ext) {
-            const uint32_t e = ws.q_ext[b][i];
+            const uint32_t e = AKB_WF_LD(ws.q_ext[b] + i);
             slot = e & kSlotMask;
             AKB_CHECK(slot < (uint32_t)ws.n_slots);
             if (e & kDeadRay) { // parked path: nothing to trace, the shade step just finishes it
                 T.hit.tri = -1, T.hit.mat = -1, T.any = false;
                 return false;
             }
-            const float4 o = ws.ray_o[slot], d = ws.ray_d[slot];
+            const float4 o = AKB_WF_LD(ws.ray_o + slot), d = AKB_WF_LD(ws.ray_d + slot);
             trav_init(T, xyz(o), xyz(d), o.w, d.w, false);
         } else {
-            slot = ws.q_sh[b][i - n_ext];
+            slot = AKB_WF_LD(ws.q_sh[b] + (i - n_ext));
             AKB_CHECK(slot < (uint32_t)ws.n_slots);
-            const float4 o = ws.sh_o[slot], d = ws.sh_d[slot];
+            const float4 o = AKB_WF_LD(ws.sh_o + slot), d = AKB_WF_LD(ws.sh_d + slot);
             trav_init(T, xyz(o), xyz(d), o.w, d.w, true);
         }
         return true;
@@ -501,16 +514,16 @@ template <int SAMP> struct WfSrc {
                     }
                 }
             } else {
-                const float4 c = ws.sh_c[slot];
+                const float4 c = AKB_WF_LD(ws.sh_c + slot);
                 if (c.w != 0.f) {
                     // last shadow ray of a sample whose pixel is already on its next one: this is the film add the
                     // shade step would have done one bounce later ("Splat", core/film.h:66-70). The pixel's next
                     // sample cannot finish before the next shade step, so the sums keep their order.
-                    const float4 a = ws.acc[slot];
-                    const v3 s = add3(xyz(a), T.hit.tri < 0 ? xyz(c) : xyz(ws.sh_b[slot]));
+                    const float4 a = AKB_WF_LD(ws.acc + slot);
+                    const v3 s = add3(xyz(a), T.hit.tri < 0 ? xyz(c) : xyz(AKB_WF_LD(ws.sh_b + slot)));
                     ws.acc[slot] = make_float4(s.x, s.y, s.z, a.w + 1.0f);
                 } else if (T.hit.tri < 0) { // unoccluded: L += color, kernel/pathtracer.h:156
-                    float4 L = ws.L[slot];
+                    float4 L = AKB_WF_LD(ws.L + slot);
                     const v3 s = add3(xyz(L), xyz(c));
                     L.x = s.x, L.y = s.y, L.z = s.z;
                     ws.L[slot] = L;
