@@ -229,7 +229,9 @@ uint64_t akb_scene_info(const akb_scene *scene, int what);
  * Film::radiance / Film::weight after merge_tile (core/film.h:66-95). `stats` may be NULL.
  * params->n_gpus >= 2: the frame is split over that many GPUs and combined on device 0 with one ncclReduce
  * (AKB_NCCL_ERROR if NCCL cannot be loaded or fails; akb_set_option("combine", "p2p") uses the library's own
- * peer-memory kernels over NVLink instead). With AKB_SPLIT_TILE the film is bit-identical to the one-GPU film. */
+ * peer-memory kernels over NVLink instead). With AKB_SPLIT_TILE the film is bit-identical to the one-GPU film.
+ * A page-locked `out_rgbw` (cudaHostAlloc / cudaHostRegister) receives the film by one DMA; pageable memory is filled
+ * through the library's own pinned staging buffer. */
 akb_status akb_render(akb_scene *scene, const akb_render_params *params, float *out_rgbw, akb_render_stats *stats);
 
 /* Same, but the film stays in HBM: `d_out_rgbw` is a DEVICE pointer (width*height*4 floats) the caller owns
@@ -240,7 +242,9 @@ akb_status akb_render_device(akb_scene *scene, const akb_render_params *params, 
 
 /* Replaces Scene::intersect / Scene::occlude (kernel/scene.h:58-67) over a batch of rays.
  * Rays are two float4 streams (vectorised SoA): org_tmin[i] = (ox,oy,oz,tmin), dir_tmax[i] = (dx,dy,dz,tmax).
- * any_hit = 0: closest hit -> out_hits[i]; any_hit = 1: out_occluded[i] = 0/1. HOST pointers. */
+ * any_hit = 0: closest hit -> out_hits[i]; any_hit = 1: out_occluded[i] = 0/1. HOST pointers. Rays go to the device in
+ * chunks (option trace_chunk) on two streams, so both PCIe directions overlap the traversal; page-locked buffers are
+ * copied from / into directly, pageable ones through the library's pinned staging slots. */
 akb_status akb_trace(akb_scene *scene, const float *org_tmin, const float *dir_tmax, size_t n_rays, int any_hit,
                      akb_hit *out_hits, int32_t *out_occluded);
 /* DEVICE-pointer variant of akb_trace; `ms_kernel` (may be NULL) receives the traversal kernel's device time. */
