@@ -62,12 +62,39 @@ AKB_HD float sincosf_glibc(float y, int is_cos) {
     }
     return is_cos ? (float)cos(x) : (float)sin(x);
 }
+// sinf(y) and cosf(y) of the same argument: the two calls above with their common part - the quadrant reduction -
+// written once. Each result is the value sincosf_glibc returns for it, statement for statement.
+AKB_HD void sincosf_glibc_both(float y, float &s, float &c) {
+    double x = (double)y;
+    if (abstop12(y) < 0x3f4u) {
+        if (abstop12(y) < 0x398u) {
+            s = y, c = 1.0f;
+            return;
+        }
+        const double x2 = x * x;
+        s = sincosf_poly(x, x2, false, 0), c = sincosf_poly(x, x2, false, 1);
+        return;
+    }
+    if (abstop12(y) < 0x42fu) {
+        const double r = x * 0x1.45F306DC9C883p+23;
+        const int n = ((int32_t)r + 0x800000) >> 24;
+        x = fma(-(double)n, 0x1.921FB54442D18p0, x);
+        const double sgn = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
+        const double xs = x * sgn, x2 = x * x;
+        const bool neg = (n & 2) != 0;
+        s = sincosf_poly(xs, x2, neg, n), c = sincosf_poly(xs, x2, neg, n ^ 1);
+        return;
+    }
+    s = (float)sin(x), c = (float)cos(x);
+}
 #if defined(__CUDA_ARCH__) && AKB_EXACT_LIBM
 AKB_HD float sin_ref(float x) { return sincosf_glibc(x, 0); }
 AKB_HD float cos_ref(float x) { return sincosf_glibc(x, 1); }
+AKB_HD void sincos_ref(float x, float &s, float &c) { sincosf_glibc_both(x, s, c); }
 #else
 AKB_HD float sin_ref(float x) { return sinf(x); }
 AKB_HD float cos_ref(float x) { return cosf(x); }
+AKB_HD void sincos_ref(float x, float &s, float &c) { s = sinf(x), c = cosf(x); }
 #endif
 
 // ---- flattened scene as the kernels see it (all pointers into HBM) ----------------------------------------
@@ -205,7 +232,9 @@ AKB_HD void concentric_disk(float ux, float uy, float &ox, float &oy) {
         r = y;
         theta = AKB_PI2 - AKB_PI4 * (x / y);
     }
-    ox = r * cos_ref(theta), oy = r * sin_ref(theta);
+    float st, ct;
+    sincos_ref(theta, st, ct);
+    ox = r * ct, oy = r * st;
 }
 AKB_HD v3 cosine_hemisphere(float ux, float uy) {
     float x, y;
@@ -247,10 +276,12 @@ AKB_HD float ggx_D(float alpha, v3 m) { // microfacet.h:74-82
     float a2 = alpha * alpha, c2 = cos2_theta(m), t2 = tan2_theta(m), at = (a2 + t2);
     return a2 / (AKB_PI * c2 * c2 * at * at);
 }
-AKB_HD float ggx_G1(float alpha, v3 v, v3 m) { // microfacet.h:84-89: theta of m, evaluated in double
-    if (dot3(v, m) * v.y <= 0) return 0.0f;
-    return (float)(2.0 / (1.0 + sqrt(1.0 + (double)(alpha * alpha * tan2_theta(m)))));
-}
+// microfacet.h:84-89: G1(v, m) = 0 if v and m disagree, else a term in the angle of m only, evaluated in double. The
+// reference evaluates that term once per direction; it is the same number both times (same alpha, same m), so it is
+// worked out once here (ggx_G1_term) and gated per direction - the double-precision square root and division are the
+// largest block of the shade kernel.
+AKB_HD float ggx_G1_term(float alpha, v3 m) { return (float)(2.0 / (1.0 + sqrt(1.0 + (double)(alpha * alpha * tan2_theta(m))))); }
+AKB_HD float ggx_G1(float term, v3 v, v3 m) { return dot3(v, m) * v.y <= 0 ? 0.0f : term; }
 AKB_HD v3 closure_evaluate(const Bsdf &b, v3 wo, v3 wi) {
     const v3 zero = mk3(0, 0, 0);
     if (b.kind == CL_DIFFUSE) { // material.h:69-74
@@ -266,8 +297,8 @@ AKB_HD v3 closure_evaluate(const Bsdf &b, v3 wo, v3 wi) {
         wh = normalize3(wh);
         if (wh.y < 0) wh = neg3(wh);
         float F = 1.0f;
-        float s = ggx_D(b.alpha, wh) * (ggx_G1(b.alpha, wo, wh) * ggx_G1(b.alpha, wi, wh)) * F /
-                  (4.0f * cosThetaI * cosThetaO);
+        const float g1 = ggx_G1_term(b.alpha, wh);
+        float s = ggx_D(b.alpha, wh) * (ggx_G1(g1, wo, wh) * ggx_G1(g1, wi, wh)) * F / (4.0f * cosThetaI * cosThetaO);
         return mk3(b.R.x * s, b.R.y * s, b.R.z * s);
     }
     return zero; // specular dielectric (extension) and the null closure evaluate to 0
@@ -286,7 +317,9 @@ AKB_HD v3 closure_sample(const Bsdf &b, float ux, float uy, v3 wo, v3 &wi, float
         float t2 = b.alpha * b.alpha * ux / (1 - ux);
         float cosTheta = 1.0f / sqrtf(1 + t2);
         float sinTheta = sqrtf(max_std(0.0f, 1 - cosTheta * cosTheta));
-        v3 wh = mk3(cos_ref(phi) * sinTheta, cosTheta, sin_ref(phi) * sinTheta);
+        float sp, cp;
+        sincos_ref(phi, sp, cp);
+        v3 wh = mk3(cp * sinTheta, cosTheta, sp * sinTheta);
         if (!same_hemisphere(wo, wh)) wh = neg3(wh);
         wi = reflect3(wo, wh);
         if (!same_hemisphere(wo, wi)) {
