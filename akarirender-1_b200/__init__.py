@@ -32,7 +32,7 @@ _initialised = None
 # Development aid of THIS Python layer (the library itself never reads the environment): AKB_<OPTION>=value variables
 # are forwarded once to akb_set_option, so A/B scripts can flip a switch without editing code. tests use set_option().
 _ENV_OPTIONS = ("pipelines", "pipeline_min_slots", "graphs", "check_every", "poll_lag", "finish_div", "finish_max",
-                "no_park", "shade_partition", "tail_share", "refill_below", "fetch_chunk", "profile_stages", "timeline", "trace_chunk", "trav_ifif",
+                "no_park", "shade_partition", "tail_share", "tail_share_min", "refill_below", "fetch_chunk", "profile_stages", "timeline", "trace_chunk", "trav_ifif",
                 "bvh_build", "bvh_verbose", "bvh_trav_cost", "bvh_prim_cost", "bvh_max_leaf", "bvh_device_algo",
                 "ploc_radius", "combine", "nvtx", "stream", "stream_flex_mask", "stream_watchdog_ms")
 _env_forwarded = False

@@ -381,7 +381,7 @@ akb_status push_device_options() {
         CU(set_refill_below(o.refill_below));
         CU(set_no_park(o.no_park));
         CU(set_shade_partition(o.shade_partition));
-        CU(set_tail_share(o.tail_share));
+        CU(set_tail_share(o.tail_share, o.tail_share_min));
         CU(set_fetch_chunk(o.fetch_chunk));
         CU(set_stream_options(o.stream_flex_mask, o.stream_watchdog_ms));
     }

@@ -95,7 +95,8 @@ __constant__ int c_no_park = 1; // 0 (AKB_NO_PARK=0): a path that ends with a sh
 #define g_no_park c_no_park
 __constant__ int c_fetch_chunk = 0; // 0: reserve exactly the idle-lane count per refill; >0: warp-private chunks (AKB_FETCH_CHUNK)
 __constant__ int c_shade_partition = 0; // 1 (option shade_partition): a block regroups its 128 entries into hits | misses before shading (measured slower)
-__constant__ int c_tail_share = 1; // option tail_share: 0 never, 1 in launches of >= 4 rays per thread, 2 always: a drained warp's idle lanes help its busy ones
+__constant__ int c_tail_share = 1; // option tail_share: 0 never, 1 in launches of >= tail_share_min rays per 8 threads, 2 always: a drained warp's idle lanes help its busy ones
+__constant__ int c_tail_share_min = 16; // option tail_share_min, in rays per 8 threads of the launch (16 = two rays per thread)
 __constant__ int c_refill_below = 0; // > 0: AKB_REFILL_BELOW override; else 24 with the if-if step, 20 with the fused one (measured best on B200)
 
 // The tail of a traversal launch. Once the queue is drained a warp cannot refill its idle lanes, and the launch lasts
@@ -223,11 +224,12 @@ __device__ __forceinline__ void persistent_trace(const float4 *__restrict__ node
         // (Batching the leaf-triangle tests across lanes - one Moeller-Trumbore round per iteration, or only once N
         // lanes wait - was measured on B200 and did not pay: the node block then runs with fewer lanes (20 instead of
         // 26 of 32) and total issued instructions stay within 5 %; profiles/r01c_notes.md.)
-        // (only for launches with at least four rays per thread, or option tail_share = 2: a launch with one or two rays per
-        // thread is all tail, and there the helpers' extra node fetches cost more than the shorter chains win - measured
-        // on a 1/8 tile-split share of C3: 34.4 vs 29.9 ms; full frame: 27.8 vs 28.3 ms; 2 M incoherent rays: +5 % closest,
-        // +10 % any hit)
-        if (no_more && post_limit >= 0 && (c_tail_share == 2 || (c_tail_share == 1 && total >= 4u * gridDim.x * blockDim.x))) {
+        // (only for launches with at least two rays per thread - option tail_share_min - or option tail_share = 2: a
+        // launch with fewer is all tail, and there the helpers' extra node fetches cost more than the shorter chains
+        // win. Measured, threshold in rays per thread 4 / 2 / 1 / 0.5: C3 frame 105.8 / 104.5 / 104.1 / 104.1 ms, C5
+        // 59.9 / 59.2 / 59.1 / 59.0 ms, a 1/8 tile-split share of C3 29.3 / 29.2 / 34.6 / 34.1 ms; 2 M incoherent rays:
+        // +5 % closest, +10 % any hit)
+        if (no_more && post_limit >= 0 && (c_tail_share == 2 || (c_tail_share == 1 && 8ull * total >= (unsigned long long)c_tail_share_min * gridDim.x * blockDim.x))) {
             src.complete(have, item, tag, T); // entries the refill above found ready (parked paths)
             have = false;
             tail_share(nodes, tris, src, T, stack, active, item, tag, post_limit);
@@ -1177,7 +1179,11 @@ cudaError_t set_debug_bounds(uint32_t n_nodes, uint32_t n_tris) {
 }
 cudaError_t set_refill_below(int v) { return cudaMemcpyToSymbol(c_refill_below, &v, sizeof(int)); }
 cudaError_t set_no_park(int v) { return cudaMemcpyToSymbol(c_no_park, &v, sizeof(int)); }
-cudaError_t set_tail_share(int v) { return cudaMemcpyToSymbol(c_tail_share, &v, sizeof(int)); }
+cudaError_t set_tail_share(int v, int min_rays_per_8_threads) {
+    cudaError_t e = cudaMemcpyToSymbol(c_tail_share, &v, sizeof(int));
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_tail_share_min, &min_rays_per_8_threads, sizeof(int));
+    return e;
+}
 cudaError_t set_shade_partition(int v) { return cudaMemcpyToSymbol(c_shade_partition, &v, sizeof(int)); }
 cudaError_t set_fetch_chunk(int v) { return cudaMemcpyToSymbol(c_fetch_chunk, &v, sizeof(int)); }
 

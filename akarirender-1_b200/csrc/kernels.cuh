@@ -75,7 +75,7 @@ cudaError_t set_refill_below(int v);
 cudaError_t set_debug_bounds(uint32_t n_nodes, uint32_t n_tris); // -DAKB_DEBUG_CHECKS builds only; a no-op otherwise
 cudaError_t set_fetch_chunk(int v);
 cudaError_t set_no_park(int v);
-cudaError_t set_tail_share(int v);
+cudaError_t set_tail_share(int v, int min_rays_per_8_threads);
 cudaError_t set_shade_partition(int v);
 cudaError_t launch_trace_batch(const SceneDev &S, const float4 *org, const float4 *dir, size_t n, int any_hit,
                                akb_hit *hits, int32_t *occ, uint32_t *fetch_cursor, int n_sms, cudaStream_t st);

@@ -20,7 +20,9 @@ struct Options {
     int no_park = 1;                     // 0: a path that ends with a shadow ray pending always waits one bounce for it
     int shade_partition = 0;             // 1: the shade step regroups a block's 128 entries into hits | misses (measured slower)
     int tail_share = 1;                  // once the ray queue is drained, a warp's idle lanes take subtrees off its busy lanes' stacks:
-                                         // 0 never, 1 in launches with >= 4 rays per thread, 2 always
+                                         // 0 never, 1 in launches with >= tail_share_min rays per 8 threads, 2 always
+    int tail_share_min = 16;             // (16 = two rays per thread: C3 104.5 ms against 105.8 at 32 and 104.1 at 4; a 1/8 tile-split
+                                         //  share 29.2 ms at 16 and 32 but 34.6 at 8 - launches with under two rays per thread are all tail)
     int refill_below = 0;                // persistent traversal warps refill below this many live lanes (0: 24 / 20 by step)
     int fetch_chunk = 0;                 // >0: warp-private fetch chunks
     int stream = 0;                      // 1: the streaming wavefront (one persistent launch per share, no barrier between bounces; kernels.cu)

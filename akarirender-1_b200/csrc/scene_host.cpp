@@ -335,6 +335,7 @@ bool set_option(const char *name, const char *value, std::string *err) {
     AKB_INT_OPT(no_park, 0, 1)
     AKB_INT_OPT(shade_partition, 0, 1)
     AKB_INT_OPT(tail_share, 0, 2)
+    AKB_INT_OPT(tail_share_min, 0, 1 << 20)
     AKB_INT_OPT(refill_below, 0, 32)
     AKB_INT_OPT(fetch_chunk, 0, 4096)
     AKB_INT_OPT(stream, 0, 1)
