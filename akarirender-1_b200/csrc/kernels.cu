@@ -32,6 +32,9 @@ constexpr int kBlock = AKB_BLOCK;
 #ifndef AKB_SHADE_MIN_BLOCKS
 #define AKB_SHADE_MIN_BLOCKS 7 // shade kernel: 72 registers; measured 4 / 5 / 6 / 7 / 8 blocks: C3 shade stage 8.58 / 7.69 / 7.32 / 7.15 / 7.90 ms, frame 28.83 / 28.18 / 28.12 / 27.59 / 28.13 ms
 #endif
+#ifndef AKB_MEGA_MIN_BLOCKS
+#define AKB_MEGA_MIN_BLOCKS 5 // megakernel: 96 registers; measured 4 / 5 / 6 / 8 blocks: C3 at 16 spp 35.5 / 33.1 / 33.8 / 34.1 ms, a 1/8 tile-split share 5.80 / 5.35 / 5.72 / 5.97 ms
+#endif
 #ifndef AKB_STREAM_MIN_BLOCKS
 #define AKB_STREAM_MIN_BLOCKS 8 // the streaming kernel holds both jobs
 #endif
@@ -312,7 +315,7 @@ __global__ void film_to_srgb8_kernel(const float4 *rgbw, size_t n, uint8_t *out)
 // Megakernel mode (Path { megakernel: true }): one thread per pixel runs GenericPathTracer::run_megakernel for all its
 // samples, exactly the loop of cpu::PathTracer::render (kernel/integrators/cpu/integrator.cpp:121-135).
 template <int SAMP>
-__global__ void __launch_bounds__(kBlock) megakernel(SceneDev S, RenderConfig rc, float4 *__restrict__ film, Counters *ctr) {
+__global__ void __launch_bounds__(kBlock, AKB_MEGA_MIN_BLOCKS) megakernel(SceneDev S, RenderConfig rc, float4 *__restrict__ film, Counters *ctr) {
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     int x = 0, y = 0;
     const bool valid = slot < rc.map.n_slots() && slot_to_pixel(rc.map, slot, x, y);
