@@ -584,7 +584,9 @@ def single_process_multi_gpu(pkg, sc, n, a, want_sha):
     out = {"api": "akb_init(%d) + akb_render(n_gpus = %d): one process, one host thread + stream per GPU in the library, one ncclReduce of the film" % (n, n),
            "scene_create_s": round(create_s, 2), "bvh_build_s": round(info["build_us"] / 1e6, 3),
            "replica_upload_s": round(info["upload_us"] / 1e6, 3)}
-    host_film = np.zeros((H, W, 4), np.float32)
+    import torch
+    host_film_t = torch.zeros((H, W, 4), dtype=torch.float32, pin_memory=True)  # page-locked: device 0's film arrives by one DMA
+    host_film = host_film_t.numpy()
     for split_name, split in (("sample", pkg.abi.SPLIT_SAMPLE), ("tile", pkg.abi.SPLIT_TILE)):
         p = sc.integrator.params(shard_tile=32, split=split)
         p.n_gpus = n
