@@ -878,6 +878,15 @@ akb_status render_on_replica(Replica *r, int width, int height, const akb_render
     if (streamed && opt.timeline)
         fprintf(stderr, "akb stream: gpu %d: %llu shade batches, %llu rays traced by shade-first warps, %llu idle polls\n", r->dev.index, r->h_stream->stat_shade_batches,
                 r->h_stream->stat_flex_rays, r->h_stream->stat_idle_polls);
+#ifdef AKB_TAIL_PROF
+    {
+        unsigned long long tp[6];
+        if (tail_prof_read(tp, true) == cudaSuccess)
+            fprintf(stderr, "akb tail prof: queue live %llu steps at %.1f lanes | drained %llu steps at %.1f lanes | tail_share %llu steps at %.1f lanes\n", tp[0],
+                    tp[1] / (double)std::max<unsigned long long>(tp[0], 1), tp[2], tp[3] / (double)std::max<unsigned long long>(tp[2], 1), tp[4],
+                    tp[5] / (double)std::max<unsigned long long>(tp[4], 1));
+    }
+#endif
 #ifdef AKB_STREAM_PROF
     if (streamed)
         for (int g = 0; g < 2; g++) {

@@ -102,6 +102,9 @@ __constant__ int c_tail_share = 1; // option tail_share: 0 never, 1 in launches 
 __constant__ int c_tail_share_min = 16; // option tail_share_min, in rays per 8 threads of the launch (16 = two rays per thread)
 __constant__ int c_refill_below = 0; // > 0: AKB_REFILL_BELOW override; else 24 with the if-if step, 20 with the fused one (measured best on B200)
 
+#ifdef AKB_TAIL_PROF
+__device__ unsigned long long g_tail_prof[6];
+#endif
 // The tail of a traversal launch. Once the queue is drained a warp cannot refill its idle lanes, and the launch lasts
 // as long as its slowest ray: one dependent chain of node visits (C3: mean 11, maximum 83 visits; 32 rays alone take
 // 70 us, 2 M rays 560 us). Here the lanes that have run out of rays take pending subtrees off the traversal stacks of
@@ -119,6 +122,10 @@ __device__ __forceinline__ void tail_share(const float4 *__restrict__ nodes, con
     int root = -1;                         // >= 0: this lane is helping lane `root` with its ray
     bool own_done = false, h_done = false; // owner finished its own share and waits for helpers / helper has a result to hand back
     for (;;) {
+#ifdef AKB_TAIL_PROF
+        if (lane == 0) atomicAdd(&g_tail_prof[4], 1ull), atomicAdd(&g_tail_prof[5], (unsigned long long)__popc(__ballot_sync(full, active)));
+        else __ballot_sync(full, active);
+#endif
         if (trav_step_ii(T, nodes, tris, stack, active, post_limit)) {
             active = false;
             if (root >= 0)
@@ -239,6 +246,9 @@ __device__ __forceinline__ void persistent_trace(const float4 *__restrict__ node
             break; // every lane's ray is finished and consumed
         }
         do {
+#ifdef AKB_TAIL_PROF
+            if (lane == 0) atomicAdd(&g_tail_prof[no_more ? 2 : 0], 1ull), atomicAdd(&g_tail_prof[no_more ? 3 : 1], (unsigned long long)__popc(act));
+#endif
             // post_limit >= 0: the "if-if" step (one node visit + one triangle test per lane and iteration, traverse.h);
             // < 0: the fused step, which is better for tiny trees where a ray is a handful of steps
             if (post_limit >= 0 ? trav_step_ii(T, nodes, tris, stack, active, post_limit) : (active && trav_step(T, nodes, tris, stack)))
@@ -1180,6 +1190,16 @@ cudaError_t set_debug_bounds(uint32_t n_nodes, uint32_t n_tris) {
     return cudaSuccess;
 #endif
 }
+#ifdef AKB_TAIL_PROF
+cudaError_t tail_prof_read(unsigned long long *out6, bool reset) {
+    cudaError_t e = cudaMemcpyFromSymbol(out6, g_tail_prof, 6 * sizeof(unsigned long long));
+    if (e == cudaSuccess && reset) {
+        const unsigned long long z[6] = {};
+        e = cudaMemcpyToSymbol(g_tail_prof, z, sizeof z);
+    }
+    return e;
+}
+#endif
 cudaError_t set_refill_below(int v) { return cudaMemcpyToSymbol(c_refill_below, &v, sizeof(int)); }
 cudaError_t set_no_park(int v) { return cudaMemcpyToSymbol(c_no_park, &v, sizeof(int)); }
 cudaError_t set_tail_share(int v, int min_rays_per_8_threads) {

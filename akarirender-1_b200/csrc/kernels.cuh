@@ -16,6 +16,7 @@ struct Counters {
     uint32_t fetch_trace;          // work-fetch cursor of the persistent traversal warps (reset by the previous kernel)
     uint32_t pad[3];
     unsigned long long stat_closest, stat_shadow, stat_samples, stat_skipped;
+    unsigned long long prof[6]; // -DAKB_TAIL_PROF builds: traversal steps / active lanes summed, [0,1] while the queue has rays, [2,3] after it is drained, [4,5] inside tail_share
 };
 
 // Control block of the streaming wavefront (option stream = 1; one struct in HBM, zeroed before every frame). Tickets
@@ -72,6 +73,9 @@ struct LaunchDims {
 
 cudaError_t launch_selftest(int *d_result, cudaStream_t st);
 cudaError_t set_refill_below(int v);
+#ifdef AKB_TAIL_PROF
+cudaError_t tail_prof_read(unsigned long long *out6, bool reset); // development: where the traversal steps of a frame go
+#endif
 cudaError_t set_debug_bounds(uint32_t n_nodes, uint32_t n_tris); // -DAKB_DEBUG_CHECKS builds only; a no-op otherwise
 cudaError_t set_fetch_chunk(int v);
 cudaError_t set_no_park(int v);
